@@ -1,0 +1,130 @@
+"""ctypes binding of the C ABI in include/fa_sm100.h (libfa_sm100.so).
+
+This is the FFI stub that stands where the reference's pybind module
+``flash_attention_extension`` stood (csrc/flash_attention_api.cpp:137-141).  There is no CPU or
+PyTorch fallback behind it: if the library cannot be built or loaded the import fails loudly.
+"""
+from __future__ import annotations
+
+import ctypes
+import threading
+from ctypes import POINTER, Structure, c_char_p, c_float, c_int32, c_int64, c_uint32, c_uint64, c_void_p
+
+from . import _build
+
+FA_SM100_FP16 = 0
+FA_SM100_BF16 = 1
+FLAG_NO_PACK_GQA = 1
+FLAG_FORCE_PACK_GQA = 2
+
+STATUS_NAMES = {
+    0: "OK",
+    1: "INVALID_ARGUMENT",
+    2: "UNSUPPORTED_DEVICE",
+    3: "CUDA",
+    4: "KERNEL_ABORT",
+}
+
+# Every symbol include/fa_sm100.h declares (tests check the library exports all of them).
+EXPORTED_SYMBOLS = (
+    "fa_sm100_fwd",
+    "fa_sm100_last_error",
+    "fa_sm100_check_device",
+    "fa_sm100_launch_count",
+    "fa_sm100_build_info",
+    "fa_sm100_plan",
+    "fa_sm100_selftest_umma",
+)
+
+
+class FwdParams(Structure):
+    """Mirror of ``struct fa_sm100_fwd_params``."""
+
+    _fields_ = [
+        ("q", c_void_p),
+        ("k", c_void_p),
+        ("v", c_void_p),
+        ("o", c_void_p),
+        ("batch", c_int64),
+        ("heads_q", c_int64),
+        ("heads_kv", c_int64),
+        ("seqlen_q", c_int64),
+        ("seqlen_kv", c_int64),
+        ("headdim", c_int64),
+        ("q_strides", c_int64 * 3),
+        ("k_strides", c_int64 * 3),
+        ("v_strides", c_int64 * 3),
+        ("o_strides", c_int64 * 3),
+        ("softmax_scale", c_float),
+        ("causal", c_int32),
+        ("dtype", c_int32),
+        ("device", c_int32),
+        ("flags", c_uint32),
+    ]
+
+
+_lock = threading.Lock()
+_lib = None
+
+
+def load() -> ctypes.CDLL:
+    """Build (if stale) and dlopen libfa_sm100.so; set up prototypes."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        path = _build.LIB
+        if not _build.is_current():
+            try:
+                path = _build.build()
+            except Exception as exc:  # no nvcc on this machine: accept a prebuilt, else fail loudly
+                if not _build.LIB.exists():
+                    raise RuntimeError(
+                        "flash_attention (sm_100a): libfa_sm100.so is missing and could not be built; "
+                        "there is no fallback implementation"
+                    ) from exc
+                path = _build.LIB
+        lib = ctypes.CDLL(str(path))
+        lib.fa_sm100_fwd.argtypes = [POINTER(FwdParams), c_void_p]
+        lib.fa_sm100_fwd.restype = c_int32
+        lib.fa_sm100_last_error.argtypes = []
+        lib.fa_sm100_last_error.restype = c_char_p
+        lib.fa_sm100_check_device.argtypes = [c_int32]
+        lib.fa_sm100_check_device.restype = c_int32
+        lib.fa_sm100_launch_count.argtypes = []
+        lib.fa_sm100_launch_count.restype = c_uint64
+        lib.fa_sm100_build_info.argtypes = []
+        lib.fa_sm100_build_info.restype = c_char_p
+        lib.fa_sm100_plan.argtypes = [POINTER(FwdParams)] + [POINTER(c_int32)] * 4
+        lib.fa_sm100_plan.restype = c_int32
+        lib.fa_sm100_selftest_umma.argtypes = [
+            c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+            c_int32, c_int32, c_float, c_uint32, c_uint32, c_int32, c_void_p,
+        ]
+        lib.fa_sm100_selftest_umma.restype = c_int32
+        _lib = lib
+        return lib
+
+
+def last_error() -> str:
+    return load().fa_sm100_last_error().decode("utf-8", "replace")
+
+
+def raise_for_status(rc: int) -> None:
+    if rc == 0:
+        return
+    msg = f"fa_sm100 [{STATUS_NAMES.get(rc, rc)}]: {last_error()}"
+    if rc == 1:
+        raise RuntimeError(msg)  # the reference raises RuntimeError from TORCH_CHECK
+    raise RuntimeError(msg)
+
+
+def launch_count() -> int:
+    return int(load().fa_sm100_launch_count())
+
+
+def check_device(device: int) -> None:
+    """Synchronise and raise if an in-kernel watchdog fired (tests / smoke)."""
+    raise_for_status(load().fa_sm100_check_device(int(device)))

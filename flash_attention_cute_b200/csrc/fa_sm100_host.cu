@@ -1,0 +1,350 @@
+// Host side of the C ABI declared in include/fa_sm100.h: argument validation (the checks of
+// reference csrc/flash_attention_api.cpp:17-59), variant selection (replaces
+// csrc/kernel_dispatcher.h:20-52 and csrc/flash_attention_impl.cu:7-49), TMA tensor-map
+// encoding, launch (replaces csrc/flash_attention_template.cuh:567-583).  No torch, no CUTLASS.
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+
+#include "../../include/fa_sm100.h"
+#include "fa_sm100_kernel.cuh"
+
+namespace {
+
+thread_local char g_err[512] = "";
+std::atomic<uint64_t> g_launches{0};
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+// ---- driver entry point for cuTensorMapEncodeTiled (no link-time libcuda dependency) ----
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        cudaError_t e =
+            cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres);
+        if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess) p = nullptr;
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
+
+// ---- per-device state, created once ----
+constexpr int kMaxDevices = 64;
+struct DeviceState {
+    std::once_flag once;
+    int error = 0;
+    int cc_major = 0, cc_minor = 0, num_sms = 0, max_smem_optin = 0;
+    unsigned int* status = nullptr;  // 4 words of device memory, zeroed
+    char msg[256] = "";
+};
+DeviceState g_dev[kMaxDevices];
+
+DeviceState* device_state(int device) {
+    if (device < 0 || device >= kMaxDevices) return nullptr;
+    DeviceState* st = &g_dev[device];
+    std::call_once(st->once, [st, device] {
+        cudaError_t e;
+        int prev = 0;
+        cudaGetDevice(&prev);
+        auto check = [&](cudaError_t err, const char* what) {
+            if (err != cudaSuccess && st->error == 0) {
+                st->error = FA_SM100_ERR_CUDA;
+                snprintf(st->msg, sizeof(st->msg), "%s: %s", what, cudaGetErrorString(err));
+            }
+        };
+        e = cudaSetDevice(device);
+        check(e, "cudaSetDevice");
+        if (e == cudaSuccess) {
+            check(cudaDeviceGetAttribute(&st->cc_major, cudaDevAttrComputeCapabilityMajor, device), "attr");
+            check(cudaDeviceGetAttribute(&st->cc_minor, cudaDevAttrComputeCapabilityMinor, device), "attr");
+            check(cudaDeviceGetAttribute(&st->num_sms, cudaDevAttrMultiProcessorCount, device), "attr");
+            check(cudaDeviceGetAttribute(&st->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device), "attr");
+            check(cudaMalloc(&st->status, 4 * sizeof(unsigned int)), "cudaMalloc(status)");
+            if (st->status) check(cudaMemset(st->status, 0, 4 * sizeof(unsigned int)), "cudaMemset(status)");
+        }
+        cudaSetDevice(prev);
+    });
+    return st;
+}
+
+// ---- variant table ----
+using KernelFn = void (*)(const fa100::KernelParams);
+struct Variant {
+    KernelFn fn;
+    int smem_bytes;
+    std::once_flag attr_once[kMaxDevices];
+};
+
+template <int kD, bool kBf16, int kStages>
+Variant* variant() {
+    static Variant v{fa100::fa_fwd_sm100_kernel<kD, kBf16, kStages>,
+                     fa100::SmemLayout<kD, kStages>::kDynamicBytes};
+    return &v;
+}
+
+constexpr int kStages128 = 5;  // 2 x 32 KB Q + 5 x 32 KB K/V = 224 KB
+constexpr int kStages64 = 8;   // 2 x 16 KB Q + 8 x 16 KB K/V = 160 KB
+
+Variant* pick_variant(int kd, bool bf16) {
+    if (kd == 128) return bf16 ? variant<128, true, kStages128>() : variant<128, false, kStages128>();
+    return bf16 ? variant<64, true, kStages64>() : variant<64, false, kStages64>();
+}
+
+struct Plan {
+    int kd;             // kernel head-dim variant (64 or 128)
+    int pack_g;         // 1 = unpacked
+    int rows_per_head;  // P
+    int num_m_blocks;
+    int head_units;
+    int grid;
+    Variant* var;
+};
+
+int validate_and_plan(const fa_sm100_fwd_params* p, Plan* plan) {
+    if (!p) return fail(FA_SM100_ERR_INVALID_ARGUMENT, "params is NULL");
+    if (!p->q || !p->k || !p->v || !p->o)
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT, "q, k, v, o must be non-NULL device pointers");
+    // messages mirror reference csrc/flash_attention_api.cpp:22-55
+    if (p->batch <= 0 || p->heads_q <= 0 || p->seqlen_q <= 0 || p->headdim <= 0 ||
+        p->heads_kv <= 0 || p->seqlen_kv <= 0)
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT, "q, k, v must have at least one element");
+    if (p->heads_q < p->heads_kv)
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT,
+                    "number of heads in q must be greater or equal to number of heads in k and v");
+    if (p->heads_q % p->heads_kv != 0)
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT,
+                    "number of heads in q must be multiple of number of heads in k and v");
+    if (p->dtype != FA_SM100_FP16 && p->dtype != FA_SM100_BF16)
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT, "q, k, v only support fp16 or bf16 data type");
+    if (p->headdim % 8 != 0)
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT, "hidden dimension must be multiple of 8");
+    if (p->headdim > 128)
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT, "only support hidden dimension <= 128");
+    if (p->seqlen_q > (1ll << 30) || p->seqlen_kv > (1ll << 30) || p->batch > 65535 * 16 ||
+        p->heads_q > 65535)
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT, "problem size out of range");
+    auto aligned16 = [](const void* ptr) { return (reinterpret_cast<uintptr_t>(ptr) & 15u) == 0; };
+    if (!aligned16(p->q) || !aligned16(p->k) || !aligned16(p->v) || !aligned16(p->o))
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT, "q, k, v, o must be 16-byte aligned");
+    auto strides_ok = [](const int64_t* s, const int64_t* dims) {
+        for (int i = 0; i < 3; ++i)
+            if (dims[i] > 1 && (s[i] <= 0 || s[i] % 8 != 0)) return false;
+        return true;
+    };
+    const int64_t qd[3] = {p->batch, p->heads_q, p->seqlen_q};
+    const int64_t kd[3] = {p->batch, p->heads_kv, p->seqlen_kv};
+    if (!strides_ok(p->q_strides, qd) || !strides_ok(p->k_strides, kd) ||
+        !strides_ok(p->v_strides, kd) || !strides_ok(p->o_strides, qd))
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT,
+                    "batch/head/sequence strides must be positive multiples of 8 elements (16 bytes)");
+
+    const int group = int(p->heads_q / p->heads_kv);
+    plan->kd = p->headdim <= 64 ? 64 : 128;
+    bool pack = group > 1 && group <= 128;
+    if (p->flags & FA_SM100_FLAG_NO_PACK_GQA) pack = false;
+    // Heuristic: packing pays when one head alone cannot fill the CTA's 256 query rows; for long
+    // prefill both mappings do the same MMA work and the unpacked one has the simpler mask.
+    if (pack && !(p->flags & FA_SM100_FLAG_FORCE_PACK_GQA) && p->seqlen_q >= 256) pack = false;
+    plan->pack_g = pack ? group : 1;
+    plan->rows_per_head = pack ? 128 / group : 128;
+    plan->num_m_blocks = int((p->seqlen_q + 2 * plan->rows_per_head - 1) / (2 * plan->rows_per_head));
+    plan->head_units = int(pack ? p->heads_kv : p->heads_q);
+    const int64_t grid = int64_t(plan->num_m_blocks) * plan->head_units * p->batch;
+    if (grid > 0x7fffffffll) return fail(FA_SM100_ERR_INVALID_ARGUMENT, "grid too large");
+    plan->grid = int(grid);
+    plan->var = pick_variant(plan->kd, p->dtype == FA_SM100_BF16);
+    return FA_SM100_OK;
+}
+
+int encode_map(CUtensorMap* map, CUtensorMapDataType dt, int rank, const void* base,
+               const cuuint64_t* dims, const cuuint64_t* strides_bytes, const cuuint32_t* box,
+               const char* what) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) return fail(FA_SM100_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+    CUresult r = fn(map, dt, cuuint32_t(rank), const_cast<void*>(base), dims, strides_bytes, box,
+                    estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return fail(FA_SM100_ERR_CUDA, "cuTensorMapEncodeTiled(%s) failed with CUresult %d", what, int(r));
+    return FA_SM100_OK;
+}
+
+// A size-1 dimension may carry any stride in torch; TMA still wants a 16 B multiple.
+inline cuuint64_t stride_bytes(int64_t stride_elems, int64_t dim, cuuint64_t fallback) {
+    if (dim <= 1 || stride_elems <= 0) return fallback;
+    return cuuint64_t(stride_elems) * 2;
+}
+
+}  // namespace
+
+extern "C" const char* fa_sm100_last_error(void) { return g_err; }
+
+extern "C" uint64_t fa_sm100_launch_count(void) { return g_launches.load(); }
+
+extern "C" const char* fa_sm100_build_info(void) {
+    return "fa_sm100: sm_100a tcgen05/TMEM/TMA FlashAttention-2 forward; variants D{64,128} x "
+           "{fp16,bf16}; 320 threads/CTA, 2x128-row M tiles, 128-col KV blocks";
+}
+
+extern "C" int fa_sm100_plan(const fa_sm100_fwd_params* params, int32_t* grid, int32_t* smem_bytes,
+                             int32_t* pack_g, int32_t* rows_per_head) {
+    Plan plan;
+    int rc = validate_and_plan(params, &plan);
+    if (rc) return rc;
+    if (grid) *grid = plan.grid;
+    if (smem_bytes) *smem_bytes = plan.var->smem_bytes;
+    if (pack_g) *pack_g = plan.pack_g;
+    if (rows_per_head) *rows_per_head = plan.rows_per_head;
+    return FA_SM100_OK;
+}
+
+extern "C" int fa_sm100_fwd(const fa_sm100_fwd_params* p, void* stream) {
+    Plan plan;
+    int rc = validate_and_plan(p, &plan);
+    if (rc) return rc;
+
+    DeviceState* st = device_state(p->device);
+    if (!st) return fail(FA_SM100_ERR_INVALID_ARGUMENT, "bad device ordinal %d", p->device);
+    if (st->error) return fail(st->error, "device init failed: %s", st->msg);
+    if (st->cc_major != 10)
+        return fail(FA_SM100_ERR_UNSUPPORTED_DEVICE,
+                    "fa_sm100 needs an sm_100 (B200) GPU; device %d is sm_%d%d — there is no fallback",
+                    p->device, st->cc_major, st->cc_minor);
+
+    int prev = 0;
+    cudaGetDevice(&prev);
+    if (prev != p->device) cudaSetDevice(p->device);
+    struct Restore {
+        int prev, cur;
+        ~Restore() { if (prev != cur) cudaSetDevice(prev); }
+    } restore{prev, p->device};
+
+    Variant* var = plan.var;
+    if (var->smem_bytes > st->max_smem_optin)
+        return fail(FA_SM100_ERR_UNSUPPORTED_DEVICE, "kernel needs %d B shared memory, device allows %d",
+                    var->smem_bytes, st->max_smem_optin);
+    cudaError_t attr_err = cudaSuccess;
+    std::call_once(var->attr_once[p->device], [&] {
+        attr_err = cudaFuncSetAttribute(reinterpret_cast<const void*>(var->fn),
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, var->smem_bytes);
+    });
+    if (attr_err != cudaSuccess)
+        return fail(FA_SM100_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(attr_err));
+
+    fa100::KernelParams kp;
+    memset(&kp, 0, sizeof(kp));
+    const CUtensorMapDataType dt =
+        p->dtype == FA_SM100_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+    const int group = int(p->heads_q / p->heads_kv);
+    const cuuint64_t D = cuuint64_t(p->headdim);
+    {
+        // Q as (d, s, g, hkv, b): head h = hkv * G + g
+        const cuuint64_t row = D * 2;
+        cuuint64_t s_s = stride_bytes(p->q_strides[2], p->seqlen_q, row);
+        cuuint64_t s_g = stride_bytes(p->q_strides[1], p->heads_q, s_s * cuuint64_t(p->seqlen_q));
+        cuuint64_t s_h = s_g * cuuint64_t(group);
+        cuuint64_t s_b = stride_bytes(p->q_strides[0], p->batch, s_h * cuuint64_t(p->heads_kv));
+        cuuint64_t dims[5] = {D, cuuint64_t(p->seqlen_q), cuuint64_t(group), cuuint64_t(p->heads_kv),
+                              cuuint64_t(p->batch)};
+        cuuint64_t strides[4] = {s_s, s_g, s_h, s_b};
+        cuuint32_t box[5] = {64, cuuint32_t(plan.rows_per_head), cuuint32_t(plan.pack_g), 1, 1};
+        rc = encode_map(&kp.tm_q, dt, 5, p->q, dims, strides, box, "q");
+        if (rc) return rc;
+    }
+    auto encode_kv = [&](CUtensorMap* m, const void* base, const int64_t* es, const char* what) {
+        const cuuint64_t row = D * 2;
+        cuuint64_t s_s = stride_bytes(es[2], p->seqlen_kv, row);
+        cuuint64_t s_h = stride_bytes(es[1], p->heads_kv, s_s * cuuint64_t(p->seqlen_kv));
+        cuuint64_t s_b = stride_bytes(es[0], p->batch, s_h * cuuint64_t(p->heads_kv));
+        cuuint64_t dims[4] = {D, cuuint64_t(p->seqlen_kv), cuuint64_t(p->heads_kv), cuuint64_t(p->batch)};
+        cuuint64_t strides[3] = {s_s, s_h, s_b};
+        cuuint32_t box[4] = {64, 128, 1, 1};
+        return encode_map(m, dt, 4, base, dims, strides, box, what);
+    };
+    rc = encode_kv(&kp.tm_k, p->k, p->k_strides, "k");
+    if (rc) return rc;
+    rc = encode_kv(&kp.tm_v, p->v, p->v_strides, "v");
+    if (rc) return rc;
+
+    kp.o = p->o;
+    kp.o_stride_b = p->o_strides[0];
+    kp.o_stride_h = p->o_strides[1];
+    kp.o_stride_s = p->o_strides[2];
+    kp.batch = int(p->batch);
+    kp.heads_q = int(p->heads_q);
+    kp.heads_kv = int(p->heads_kv);
+    kp.group = group;
+    kp.seqlen_q = int(p->seqlen_q);
+    kp.seqlen_k = int(p->seqlen_kv);
+    kp.headdim = int(p->headdim);
+    kp.pack_g = plan.pack_g;
+    kp.rows_per_head = plan.rows_per_head;
+    kp.num_m_blocks = plan.num_m_blocks;
+    kp.head_units = plan.head_units;
+    kp.q_tile_bytes = (plan.kd / 64) * 64 * plan.rows_per_head * plan.pack_g * 2;
+    kp.causal = p->causal ? 1 : 0;
+    kp.scale_log2 = p->softmax_scale * float(M_LOG2E);
+    kp.status = st->status;
+
+    var->fn<<<dim3(plan.grid), dim3(fa100::kNumThreads), var->smem_bytes,
+              static_cast<cudaStream_t>(stream)>>>(kp);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(FA_SM100_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(e));
+    g_launches.fetch_add(1);
+    return FA_SM100_OK;
+}
+
+extern "C" int fa_sm100_check_device(int device) {
+    DeviceState* st = device_state(device);
+    if (!st) return fail(FA_SM100_ERR_INVALID_ARGUMENT, "bad device ordinal %d", device);
+    if (st->error) return fail(st->error, "device init failed: %s", st->msg);
+    int prev = 0;
+    cudaGetDevice(&prev);
+    cudaSetDevice(device);
+    unsigned int h[4] = {0, 0, 0, 0};
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = cudaMemcpy(h, st->status, sizeof(h), cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && h[0] != 0) cudaMemset(st->status, 0, sizeof(h));
+    cudaSetDevice(prev);
+    if (e != cudaSuccess) return fail(FA_SM100_ERR_CUDA, "device sync: %s", cudaGetErrorString(e));
+    if (h[0] != 0)
+        return fail(FA_SM100_ERR_KERNEL_ABORT,
+                    "in-kernel watchdog fired: wait site %u, block %u, thread %u, parity %u",
+                    h[0] & 0x7fffffffu, h[1], h[2], h[3]);
+    return FA_SM100_OK;
+}
+
+// Exposed for fa_sm100_selftest.cu
+extern "C" unsigned int* fa_sm100_internal_status(int device) {
+    DeviceState* st = device_state(device);
+    return (st && !st->error) ? st->status : nullptr;
+}
+extern "C" int fa_sm100_internal_encode_2d(CUtensorMap* map, int is_bf16, const void* base,
+                                           uint64_t rows, uint64_t cols) {
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {cols * 2};
+    cuuint32_t box[2] = {64, 128};
+    return encode_map(map, is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16,
+                      2, base, dims, strides, box, "selftest");
+}
+extern "C" void fa_sm100_internal_count_launch(void) { g_launches.fetch_add(1); }
+extern "C" int fa_sm100_internal_fail(int code, const char* msg) { return fail(code, "%s", msg); }

@@ -1,0 +1,119 @@
+"""Counterpart of the reference's flash_attention/load_cpp_extention.py:11-54.
+
+``load_extension()`` returns an object exposing ``flash_attention_fwd(q, k, v, softmax_scale,
+causal) -> Tensor`` — the one function the reference's pybind module ``flash_attention_extension``
+exports (csrc/flash_attention_api.cpp:137-141).  Here it is a thin host shim: the reference's
+argument checks (csrc/flash_attention_api.cpp:22-59, same messages), ``o = empty_like(q)``
+(:85, so O inherits q's strides), then one call through the C ABI ``fa_sm100_fwd`` on the
+current torch stream (:115).  PyTorch only provides device memory and the stream.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from . import _lib
+
+_DTYPES = {torch.float16: _lib.FA_SM100_FP16, torch.bfloat16: _lib.FA_SM100_BF16}
+
+
+def _check(cond: bool, msg: str) -> None:
+    if not cond:
+        raise RuntimeError(msg)
+
+
+def _tma_compatible(t: torch.Tensor) -> bool:
+    if t.data_ptr() % 16:
+        return False
+    for size, stride in zip(t.shape[:3], t.stride()[:3]):
+        if size > 1 and (stride <= 0 or stride % 8):
+            return False
+    return True
+
+
+def fill_params(q, k, v, o, softmax_scale: float, causal: bool, flags: int = 0) -> _lib.FwdParams:
+    p = _lib.FwdParams()
+    p.q, p.k, p.v, p.o = q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr()
+    p.batch, p.heads_q, p.seqlen_q, p.headdim = q.shape
+    p.heads_kv, p.seqlen_kv = k.shape[1], k.shape[2]
+    for dst, t in ((p.q_strides, q), (p.k_strides, k), (p.v_strides, v), (p.o_strides, o)):
+        dst[0], dst[1], dst[2] = t.stride(0), t.stride(1), t.stride(2)
+    p.softmax_scale = float(softmax_scale)
+    p.causal = 1 if causal else 0
+    p.dtype = _DTYPES[q.dtype]
+    if q.is_cuda:
+        p.device = q.device.index if q.device.index is not None else torch.cuda.current_device()
+    else:
+        p.device = 0
+    p.flags = int(flags)
+    return p
+
+
+class FlashAttentionExtension:
+    """Stands in for the pybind module ``flash_attention_extension``."""
+
+    name = "flash_attention_extension"
+
+    def __init__(self) -> None:
+        self._lib = _lib.load()
+
+    def flash_attention_fwd(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor,
+                            softmax_scale: float, causal: bool, flags: int = 0) -> torch.Tensor:
+        # --- the reference's checks, csrc/flash_attention_api.cpp:22-59 ---
+        _check(q.dim() == 4 and k.dim() == 4 and v.dim() == 4, "q, k, v must be 4-D [batch, heads, seq, dim]")
+        _check(q.size(0) == k.size(0) and q.size(0) == v.size(0), "q, k, v must have the same batch size")
+        _check(k.size(1) == v.size(1), "k, v must have the same number of heads")
+        _check(k.size(2) == v.size(2), "k, v must have the same sequence length")
+        _check(q.size(3) == k.size(3) and q.size(3) == v.size(3), "q, k, v must have the same hidden dimension")
+        _check(q.size(0) > 0 and q.size(1) > 0 and q.size(2) > 0 and q.size(3) > 0,
+               "q, k, v must have at least one element")
+        _check(k.size(1) > 0 and k.size(2) > 0, "q, k, v must have at least one element")
+        _check(q.size(1) >= k.size(1),
+               "number of heads in q must be greater or equal to number of heads in k and v")
+        _check(q.size(1) % k.size(1) == 0,
+               "number of heads in q must be multiple of number of heads in k and v")
+        _check(q.dtype == k.dtype and q.dtype == v.dtype, "q, k, v must have the same data type")
+        _check(q.dtype in _DTYPES, "q, k, v only support fp16 or bf16 data type")
+        _check(q.stride(3) == 1, "q must be contiguous in the last dimension")
+        _check(k.stride(3) == 1, "k must be contiguous in the last dimension")
+        _check(v.stride(3) == 1, "v must be contiguous in the last dimension")
+        _check(q.size(3) % 8 == 0, "hidden dimension must be multiple of 8")
+        _check(q.size(3) <= 128, "only support hidden dimension <= 128")
+        _check(q.is_cuda and k.is_cuda and v.is_cuda, "q, k, v must be on CUDA device")
+        _check(q.device == k.device and q.device == v.device, "q, k, v must be on the same CUDA device")
+
+        # TMA needs 16-byte aligned bases and strides; anything else gets one contiguous copy.
+        if not _tma_compatible(q):
+            q = q.contiguous()
+        if not _tma_compatible(k):
+            k = k.contiguous()
+        if not _tma_compatible(v):
+            v = v.contiguous()
+        o = torch.empty_like(q)  # csrc/flash_attention_api.cpp:85 — O keeps q's strides
+        if not _tma_compatible(o) or o.stride(3) != 1:
+            o = torch.empty(q.shape, dtype=q.dtype, device=q.device)
+
+        params = fill_params(q, k, v, o, softmax_scale, causal, flags)
+        stream = torch.cuda.current_stream(q.device).cuda_stream
+        rc = self._lib.fa_sm100_fwd(ctypes.byref(params), ctypes.c_void_p(stream))
+        _lib.raise_for_status(rc)
+        return o
+
+    def plan(self, q, k, v, causal: bool = False, flags: int = 0) -> dict:
+        """Describe the launch fa_sm100_fwd would do (no launch; works without a GPU)."""
+        params = fill_params(q, k, v, q, 1.0, causal, flags)
+        out = [ctypes.c_int32() for _ in range(4)]
+        rc = self._lib.fa_sm100_plan(ctypes.byref(params), *[ctypes.byref(x) for x in out])
+        _lib.raise_for_status(rc)
+        return dict(zip(("grid", "smem_bytes", "pack_g", "rows_per_head"), (x.value for x in out)))
+
+
+_ext = None
+
+
+def load_extension() -> FlashAttentionExtension:
+    global _ext
+    if _ext is None:
+        _ext = FlashAttentionExtension()
+    return _ext

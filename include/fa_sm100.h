@@ -1,0 +1,116 @@
+/*
+ * fa_sm100.h — C ABI of the B200 (sm_100a) FlashAttention-2 forward operator.
+ *
+ * This is the drop-in boundary for the reference's hot path.  It replaces, one for one,
+ *
+ *   torch::Tensor flash_attention_fwd(Tensor& q, Tensor& k, Tensor& v, float softmax_scale, bool causal)
+ *       -- reference csrc/flash_attention_api.cpp:14-135 (pybind at :137-141), and below it
+ *   struct FlashAttentionParams            -- reference csrc/flash_attention.h:5-37
+ *   run_flash_attention<T,kHeaddim,Causal> -- reference csrc/flash_attention.h:40-41,
+ *                                             csrc/flash_attention_impl.cu:30-49
+ *   type/bool/headdim dispatchers          -- reference csrc/kernel_dispatcher.h:20-52
+ *
+ * with plain pointers and sizes: no torch types, no C++ in the signatures.  The caller owns
+ * q, k, v and o (o must be allocated by the caller with the shape of q; the reference uses
+ * empty_like(q), so o normally has q's strides — any strides with unit last-dim stride are
+ * accepted).  All calls are asynchronous on `stream`, never synchronise the device, never
+ * allocate, and never call exit().  Errors come back as a non-zero status plus a thread-local
+ * message from fa_sm100_last_error().
+ *
+ * Semantics (identical to the reference):
+ *   layout  q [B, Hq, Sq, D], k/v [B, Hkv, Sk, D], o [B, Hq, Sq, D]; strides in ELEMENTS,
+ *           last-dim stride must be 1 (csrc/flash_attention_api.cpp:44-49)
+ *   dtype   fp16 or bf16, fp32 accumulation, P rounded to the input dtype before P·V
+ *   GQA     q-head h reads kv-head h / (Hq/Hkv) (csrc/flash_attention_template.cuh:157-160)
+ *   causal  bottom-right aligned: column n is visible to row m iff n <= m + (Sk - Sq)
+ *           (csrc/mask.cuh:37-39)
+ *   scale   `softmax_scale` is the natural-base scale (e.g. D^-0.5); log2(e) is folded inside
+ *           (the reference folds it at csrc/flash_attention_api.cpp:87)
+ *   D       multiple of 8, <= 128 (csrc/flash_attention_api.cpp:52-55)
+ *   Sq == 1 the reference packs the q heads of a group and drops `causal`
+ *           (csrc/flash_attention_api.cpp:72-83); with bottom-right alignment a single query row
+ *           sees every key, so the result is the same and no special case is needed here.
+ * Difference, documented: a query row with no visible key (only possible when causal and
+ * Sq > Sk) yields zeros here; the reference yields zeros or an unnormalised mean of V depending
+ * on tile skipping.
+ */
+#ifndef FA_SM100_H_
+#define FA_SM100_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum fa_sm100_dtype { FA_SM100_FP16 = 0, FA_SM100_BF16 = 1 };
+
+enum fa_sm100_status {
+    FA_SM100_OK = 0,
+    FA_SM100_ERR_INVALID_ARGUMENT = 1, /* shape / stride / dtype / alignment check failed   */
+    FA_SM100_ERR_UNSUPPORTED_DEVICE = 2, /* not an sm_100 GPU                                */
+    FA_SM100_ERR_CUDA = 3,             /* CUDA runtime / driver error (message has detail) */
+    FA_SM100_ERR_KERNEL_ABORT = 4      /* in-kernel watchdog fired (fa_sm100_check_device) */
+};
+
+/* Flags for fa_sm100_fwd_params.flags */
+#define FA_SM100_FLAG_NO_PACK_GQA 1u   /* do not pack the q heads of a kv group into one M tile */
+#define FA_SM100_FLAG_FORCE_PACK_GQA 2u /* pack whenever Hq/Hkv > 1 (default: heuristic)        */
+
+typedef struct fa_sm100_fwd_params {
+    const void* q;      /* device pointers, 16-byte aligned */
+    const void* k;
+    const void* v;
+    void* o;
+    int64_t batch;
+    int64_t heads_q;
+    int64_t heads_kv;
+    int64_t seqlen_q;
+    int64_t seqlen_kv;
+    int64_t headdim;
+    /* element strides: [0] batch, [1] head, [2] sequence; last-dim stride is 1 */
+    int64_t q_strides[3];
+    int64_t k_strides[3];
+    int64_t v_strides[3];
+    int64_t o_strides[3];
+    float softmax_scale; /* natural scale; the kernel works in the exp2 domain internally */
+    int32_t causal;      /* 0 / 1 */
+    int32_t dtype;       /* enum fa_sm100_dtype */
+    int32_t device;      /* CUDA device ordinal owning the pointers */
+    uint32_t flags;      /* FA_SM100_FLAG_* */
+} fa_sm100_fwd_params;
+
+/* Launch the forward kernel on `stream` (a cudaStream_t passed as void*; NULL = default stream).
+ * Returns fa_sm100_status. */
+int fa_sm100_fwd(const fa_sm100_fwd_params* params, void* stream);
+
+/* Thread-local, NUL-terminated description of the last non-zero status on this thread. */
+const char* fa_sm100_last_error(void);
+
+/* Synchronises `device` and reports whether any kernel launched by this library since the last
+ * call hit its in-kernel watchdog (test / debug aid; not used on the hot path). */
+int fa_sm100_check_device(int device);
+
+/* Library / kernel introspection used by tests and bench: number of kernel launches issued by
+ * this library in this process, and a static description of the build. */
+uint64_t fa_sm100_launch_count(void);
+const char* fa_sm100_build_info(void);
+
+/* Describe the variant fa_sm100_fwd would launch for `params` (no launch): fills grid size,
+ * dynamic shared memory bytes, pack factor (1 = unpacked) and q rows per head per tile. */
+int fa_sm100_plan(const fa_sm100_fwd_params* params, int32_t* grid, int32_t* smem_bytes,
+                  int32_t* pack_g, int32_t* rows_per_head);
+
+/* UMMA/TMA primitive self-test (tests/test_primitives.py): one CTA computes S = Q·Kᵀ
+ * (128 x 128, fp32) and O = round(S * p_scale)·V (128 x D, fp32) with the same descriptors the
+ * forward kernel uses.  q, k, v: [128, D] row-major device buffers of `dtype`;
+ * s_out: [128,128] fp32; o_out: [128, D] fp32.  v_lbo / v_sbo override the V descriptor's
+ * byte offsets when non-zero. */
+int fa_sm100_selftest_umma(const void* q, const void* k, const void* v, float* s_out,
+                           float* o_out, int32_t headdim, int32_t dtype, float p_scale,
+                           uint32_t v_lbo, uint32_t v_sbo, int32_t device, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FA_SM100_H_ */
