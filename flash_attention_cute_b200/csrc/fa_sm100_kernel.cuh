@@ -49,10 +49,12 @@ constexpr int kPanelBytes = 128 * 128;  // 128 rows x 64 16-bit elements
 constexpr int kNumThreads = 384;  // 3 warpgroups: softmax 0, softmax 1, {MMA, TMA, 2 idle}
 constexpr int kMmaWarp = 8;
 constexpr int kLoadWarp = 9;
-// Register file is 16384 per SM sub-partition and each sub-partition hosts 3 of the 12 warps:
-// (2 x 224 + 64) x 32 = 16384.
-constexpr int kRegsSoftmax = 224;
-constexpr int kRegsIssue = 64;
+// setmaxnreg can only redistribute what the CTA was launched with: ptxas gives 168 registers to
+// each of the 384 threads (3 warps per SM sub-partition), so 2 x kRegsSoftmax + kRegsIssue must not
+// exceed 3 x 168 = 504 — otherwise setmaxnreg.inc blocks forever (a hang no mbarrier watchdog sees).
+constexpr int kRegsSoftmax = 216;
+constexpr int kRegsIssue = 72;
+static_assert(2 * kRegsSoftmax + kRegsIssue <= 3 * 168, "register budget exceeds launch allocation");
 constexpr float kRescaleThreshold = 8.0f;  // lazy rescale: only when the max grows by > 2^8
 
 template <int kD, int kStages>
