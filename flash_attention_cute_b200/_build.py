@@ -21,7 +21,8 @@ LIB = PKG / "libfa_sm100.so"
 STAMP = PKG / ".libfa_sm100.stamp"
 
 SOURCES = [CSRC / "fa_sm100_host.cu", CSRC / "fa_sm100_selftest.cu"]
-HEADERS = [CSRC / "fa_sm100_kernel.cuh", CSRC / "fa_sm100_ptx.cuh", ROOT / "include" / "fa_sm100.h"]
+HEADERS = [CSRC / "fa_sm100_kernel.cuh", CSRC / "fa_sm100_fwd.cuh", CSRC / "fa_sm100_fwd3.cuh", CSRC / "fa_sm100_ptx.cuh",
+           ROOT / "include" / "fa_sm100.h"]
 
 NVCC_FLAGS = [
     "-O3",
@@ -29,6 +30,7 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo",
     "--expt-relaxed-constexpr",
+    "-DFA_SM100_TUNE",
     "-Xptxas", "-v",
     "-shared",
     "-Xcompiler", "-fPIC",

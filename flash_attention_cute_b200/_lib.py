@@ -16,6 +16,20 @@ FA_SM100_FP16 = 0
 FA_SM100_BF16 = 1
 FLAG_NO_PACK_GQA = 1
 FLAG_FORCE_PACK_GQA = 2
+FLAG_KERNEL_V1 = 4  # debug: first-generation (non-persistent) kernel
+
+
+def tune_flags(emu: int | None = None, split: int | None = None, halves: int | None = None) -> int:
+    """Tuning bits of fa_sm100_fwd_params.flags (FA_SM100_TUNE builds): `emu` = exp2 evaluations per
+    4 element pairs moved to the FMA pipe (0-3), `split` = keys of P handed over first (64/96/128)."""
+    f = 0
+    if emu is not None:
+        f |= (int(emu) + 1) << 8
+    if split is not None:
+        f |= {64: 1, 96: 2, 128: 3}[int(split)] << 12
+    if halves is not None:
+        f |= int(halves) << 14
+    return f
 
 STATUS_NAMES = {
     0: "OK",

@@ -10,15 +10,19 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <mutex>
 
 #include "../../include/fa_sm100.h"
 #include "fa_sm100_kernel.cuh"
+#include "fa_sm100_fwd.cuh"
+#include "fa_sm100_fwd3.cuh"
 
 namespace {
 
 thread_local char g_err[512] = "";
 std::atomic<uint64_t> g_launches{0};
+std::atomic<uint64_t> g_sched_seq{0};
 
 int fail(int code, const char* fmt, ...) {
     va_list ap;
@@ -48,11 +52,14 @@ EncodeTiledFn get_encode_fn() {
 
 // ---- per-device state, created once ----
 constexpr int kMaxDevices = 64;
+constexpr int kSchedSlots = 256;  // launches that may be in flight at once on one device
 struct DeviceState {
     std::once_flag once;
     int error = 0;
     int cc_major = 0, cc_minor = 0, num_sms = 0, max_smem_optin = 0;
     unsigned int* status = nullptr;  // 4 words of device memory, zeroed
+    int* sched = nullptr;            // kSchedSlots x {next-tile counter, finished-CTA counter}, zeroed;
+                                     // each launch takes the next slot, the kernel re-zeroes it on exit
     char msg[256] = "";
 };
 DeviceState g_dev[kMaxDevices];
@@ -79,6 +86,8 @@ DeviceState* device_state(int device) {
             check(cudaDeviceGetAttribute(&st->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device), "attr");
             check(cudaMalloc(&st->status, 4 * sizeof(unsigned int)), "cudaMalloc(status)");
             if (st->status) check(cudaMemset(st->status, 0, 4 * sizeof(unsigned int)), "cudaMemset(status)");
+            check(cudaMalloc(&st->sched, kSchedSlots * 2 * sizeof(int)), "cudaMalloc(sched)");
+            if (st->sched) check(cudaMemset(st->sched, 0, kSchedSlots * 2 * sizeof(int)), "cudaMemset(sched)");
         }
         cudaSetDevice(prev);
     });
@@ -107,6 +116,95 @@ Variant* pick_variant(int kd, bool bf16) {
     if (kd == 128) return bf16 ? variant<128, true, kStages128>() : variant<128, false, kStages128>();
     return bf16 ? variant<64, true, kStages64>() : variant<64, false, kStages64>();
 }
+
+// ---- generation-2 kernel variants (fa_sm100_fwd.cuh) ----
+using KernelFn2 = void (*)(const fa100::FwdParams);
+struct Variant2 {
+    KernelFn2 fn;
+    int smem_bytes;
+    int threads;
+    std::once_flag attr_once[kMaxDevices];
+};
+template <int kD, bool kBf16, int kStages, int kEmu, int kSplit, int kHalves, bool kTrace>
+Variant2* variant2() {
+    static Variant2 v{fa100::v2::fa_fwd_sm100_v2<kD, kBf16, kStages, kEmu, kSplit, kHalves, kTrace>,
+                      fa100::v2::Smem<kD, kStages, kHalves>::kDynamicBytes,
+                      fa100::v2::Cfg<kHalves>::kNumThreads};
+    return &v;
+}
+// K/V ring depth: D=128 tiles are 32 KB (Q0+Q1 = 64 KB): 5 stages fit beside the 1-thread-per-row
+// softmax state, 4 beside the row-max exchange buffers of the 2-threads-per-row layout.
+template <int kD, int kHalves> constexpr int stages_for() { return kD == 64 ? 8 : (kHalves == 1 ? 5 : 4); }
+
+// Defaults (chosen from the sweeps recorded in profiles/): threads per softmax row, emulated exp2
+// pairs out of 4, split keys.
+constexpr int kDefHalves = 2, kDefEmu = 0, kDefSplit = 128;
+
+template <int kD, bool kBf16>
+Variant2* pick_tuned(int halves, int emu, int split, bool trace) {
+#ifdef FA_SM100_TUNE
+#define FA_V(H, E, S)                                                                            \
+    if (halves == H && emu == E && split == S)                                                   \
+        return trace ? variant2<kD, kBf16, stages_for<kD, H>(), E, S, H, true>()                 \
+                     : variant2<kD, kBf16, stages_for<kD, H>(), E, S, H, false>();
+    FA_V(1, 0, 64) FA_V(1, 1, 64) FA_V(1, 2, 64)
+    FA_V(1, 0, 128) FA_V(1, 1, 128) FA_V(1, 2, 128)
+    FA_V(2, 0, 128) FA_V(2, 1, 128) FA_V(2, 2, 128)
+#undef FA_V
+#endif
+    (void)halves; (void)emu; (void)split; (void)trace;
+    return nullptr;
+}
+
+// ---- generation-3 kernel variants (fa_sm100_fwd3.cuh): one M-tile per CTA ----
+template <int kD, bool kBf16, int kEmu, bool kTrace>
+Variant2* variant3() {
+    constexpr int kStages = kD == 64 ? 12 : 5;
+    static Variant2 v{fa100::v3::fa_fwd_sm100_v3<kD, kBf16, kStages, kEmu, kTrace>,
+                      fa100::v3::Smem<kD, kStages>::kDynamicBytes, fa100::v3::kNumThreads};
+    return &v;
+}
+constexpr int kDefEmu3 = 0;
+Variant2* pick_variant3(int kd, bool bf16, int emu, bool trace) {
+    if (emu < 0) emu = kDefEmu3;
+#ifdef FA_SM100_TUNE
+#define FA_V3(D, BF, E)                                                                    \
+    if (kd == D && bf16 == BF && emu == E)                                                 \
+        return trace ? variant3<D, BF, E, true>() : variant3<D, BF, E, false>();
+    FA_V3(128, true, 0) FA_V3(128, true, 1) FA_V3(128, true, 2)
+    FA_V3(64, false, 0) FA_V3(64, false, 1) FA_V3(64, false, 2)
+#undef FA_V3
+#endif
+    (void)trace;
+    if (kd == 128) return bf16 ? variant3<128, true, kDefEmu3, false>() : variant3<128, false, kDefEmu3, false>();
+    return bf16 ? variant3<64, true, kDefEmu3, false>() : variant3<64, false, kDefEmu3, false>();
+}
+
+Variant2* pick_variant2(int kd, bool bf16, int halves, int emu, int split, bool trace) {
+    if (halves < 0) halves = kDefHalves;
+    if (emu < 0) emu = kDefEmu;
+    if (split < 0 || halves == 2) split = halves == 2 ? 128 : (split < 0 ? kDefSplit : split);
+    Variant2* v = nullptr;
+    if (kd == 128 && bf16) v = pick_tuned<128, true>(halves, emu, split, trace);
+    if (kd == 64 && !bf16) v = pick_tuned<64, false>(halves, emu, split, trace);
+    if (v) return v;
+    constexpr int H = kDefHalves, E = kDefEmu, S = kDefSplit;
+    if (kd == 128)
+        return bf16 ? variant2<128, true, stages_for<128, H>(), E, S, H, false>()
+                    : variant2<128, false, stages_for<128, H>(), E, S, H, false>();
+    return bf16 ? variant2<64, true, stages_for<64, H>(), E, S, H, false>()
+                : variant2<64, false, stages_for<64, H>(), E, S, H, false>();
+}
+
+constexpr bool kDefaultGen3Static = false;  // which generation fa_sm100_fwd launches by default
+// FA_SM100_GEN=2|3 in the environment overrides the default generation (test / tuning aid).
+const bool kDefaultGen3 = [] {
+    const char* e = getenv("FA_SM100_GEN");
+    if (e && e[0] == '3') return true;
+    if (e && e[0] == '2') return false;
+    return kDefaultGen3Static;
+}();
+long long* g_trace = nullptr;  // debug timeline buffer (fa_sm100_internal_set_trace)
 
 struct Plan {
     int kd;             // kernel head-dim variant (64 or 128)
@@ -238,19 +336,37 @@ extern "C" int fa_sm100_fwd(const fa_sm100_fwd_params* p, void* stream) {
         ~Restore() { if (prev != cur) cudaSetDevice(prev); }
     } restore{prev, p->device};
 
+    const bool use_v1 = (p->flags & FA_SM100_FLAG_KERNEL_V1) != 0;
+    const int tune_emu = int((p->flags >> 8) & 0xfu) - 1;                 // -1 = default
+    static const int kSplitSel[4] = {-1, 64, 96, 128};
+    const int tune_split = kSplitSel[(p->flags >> 12) & 0x3u];
     Variant* var = plan.var;
-    if (var->smem_bytes > st->max_smem_optin)
+    const int tune_halves = int((p->flags >> 14) & 0x3u) == 0 ? -1 : int((p->flags >> 14) & 0x3u);
+    const bool use_v3 = !use_v1 && (tune_halves == 3 || (tune_halves < 0 && kDefaultGen3));
+    Variant2* var2 = use_v1 ? nullptr
+                   : use_v3 ? pick_variant3(plan.kd, p->dtype == FA_SM100_BF16, tune_emu, g_trace != nullptr)
+                            : pick_variant2(plan.kd, p->dtype == FA_SM100_BF16, tune_halves, tune_emu,
+                                            tune_split, g_trace != nullptr);
+    const int smem_bytes = use_v1 ? var->smem_bytes : var2->smem_bytes;
+    if (smem_bytes > st->max_smem_optin)
         return fail(FA_SM100_ERR_UNSUPPORTED_DEVICE, "kernel needs %d B shared memory, device allows %d",
-                    var->smem_bytes, st->max_smem_optin);
+                    smem_bytes, st->max_smem_optin);
     cudaError_t attr_err = cudaSuccess;
-    std::call_once(var->attr_once[p->device], [&] {
-        attr_err = cudaFuncSetAttribute(reinterpret_cast<const void*>(var->fn),
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, var->smem_bytes);
-    });
+    if (use_v1) {
+        std::call_once(var->attr_once[p->device], [&] {
+            attr_err = cudaFuncSetAttribute(reinterpret_cast<const void*>(var->fn),
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, var->smem_bytes);
+        });
+    } else {
+        std::call_once(var2->attr_once[p->device], [&] {
+            attr_err = cudaFuncSetAttribute(reinterpret_cast<const void*>(var2->fn),
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, var2->smem_bytes);
+        });
+    }
     if (attr_err != cudaSuccess)
         return fail(FA_SM100_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(attr_err));
 
-    fa100::KernelParams kp;
+    fa100::FwdParams kp;
     memset(&kp, 0, sizeof(kp));
     const CUtensorMapDataType dt =
         p->dtype == FA_SM100_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
@@ -298,15 +414,45 @@ extern "C" int fa_sm100_fwd(const fa_sm100_fwd_params* p, void* stream) {
     kp.headdim = int(p->headdim);
     kp.pack_g = plan.pack_g;
     kp.rows_per_head = plan.rows_per_head;
-    kp.num_m_blocks = plan.num_m_blocks;
+    kp.num_m_blocks = use_v3 ? int((p->seqlen_q + plan.rows_per_head - 1) / plan.rows_per_head) : plan.num_m_blocks;
     kp.head_units = plan.head_units;
+    kp.total_heads = plan.head_units * int(p->batch);
+    kp.num_tiles = kp.num_m_blocks * kp.total_heads;
     kp.q_tile_bytes = (plan.kd / 64) * 64 * plan.rows_per_head * plan.pack_g * 2;
     kp.causal = p->causal ? 1 : 0;
     kp.scale_log2 = p->softmax_scale * float(M_LOG2E);
     kp.status = st->status;
+    kp.trace = g_trace;
+    kp.sched = st->sched + 2 * (g_sched_seq.fetch_add(1) % kSchedSlots);
+    {
+        // L2 sections: as many consecutive (batch, head) units as keep their K+V under ~40 MB
+        // (a third of the 126 MB L2), in whole kv groups when the q heads are not packed.
+        const double kv_bytes_per_kvhead = 2.0 * double(p->seqlen_kv) * double(plan.kd) * 2.0;
+        const int units_per_kvhead = plan.pack_g > 1 ? 1 : group;
+        int kvheads = int(40.0 * 1024 * 1024 / kv_bytes_per_kvhead);
+        if (kvheads < 1) kvheads = 1;
+        long long sec = (long long)kvheads * units_per_kvhead;
+        if (sec > kp.total_heads) sec = kp.total_heads;
+        kp.section_heads = int(sec);
+    }
 
-    var->fn<<<dim3(plan.grid), dim3(fa100::kNumThreads), var->smem_bytes,
-              static_cast<cudaStream_t>(stream)>>>(kp);
+    if (use_v1) {
+        fa100::KernelParams k1;
+        memset(&k1, 0, sizeof(k1));
+        k1.tm_q = kp.tm_q; k1.tm_k = kp.tm_k; k1.tm_v = kp.tm_v;
+        k1.o = kp.o; k1.o_stride_b = kp.o_stride_b; k1.o_stride_h = kp.o_stride_h; k1.o_stride_s = kp.o_stride_s;
+        k1.batch = kp.batch; k1.heads_q = kp.heads_q; k1.heads_kv = kp.heads_kv; k1.group = kp.group;
+        k1.seqlen_q = kp.seqlen_q; k1.seqlen_k = kp.seqlen_k; k1.headdim = kp.headdim;
+        k1.pack_g = kp.pack_g; k1.rows_per_head = kp.rows_per_head; k1.num_m_blocks = kp.num_m_blocks;
+        k1.head_units = kp.head_units; k1.q_tile_bytes = kp.q_tile_bytes; k1.causal = kp.causal;
+        k1.scale_log2 = kp.scale_log2; k1.status = kp.status;
+        var->fn<<<dim3(plan.grid), dim3(fa100::kNumThreads), var->smem_bytes,
+                  static_cast<cudaStream_t>(stream)>>>(k1);
+    } else {
+        const int grid = kp.num_tiles < st->num_sms ? kp.num_tiles : st->num_sms;
+        var2->fn<<<dim3(grid), dim3(var2->threads), var2->smem_bytes,
+                   static_cast<cudaStream_t>(stream)>>>(kp);
+    }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(FA_SM100_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(e));
     g_launches.fetch_add(1);
@@ -323,12 +469,15 @@ extern "C" int fa_sm100_check_device(int device) {
     unsigned int h[4] = {0, 0, 0, 0};
     cudaError_t e = cudaDeviceSynchronize();
     if (e == cudaSuccess) e = cudaMemcpy(h, st->status, sizeof(h), cudaMemcpyDeviceToHost);
-    if (e == cudaSuccess && h[0] != 0) cudaMemset(st->status, 0, sizeof(h));
+    if (e == cudaSuccess && h[0] != 0) {
+        cudaMemset(st->status, 0, sizeof(h));
+        cudaMemset(st->sched, 0, kSchedSlots * 2 * sizeof(int));  // an aborted kernel leaves its slot dirty
+    }
     cudaSetDevice(prev);
     if (e != cudaSuccess) return fail(FA_SM100_ERR_CUDA, "device sync: %s", cudaGetErrorString(e));
     if (h[0] != 0)
         return fail(FA_SM100_ERR_KERNEL_ABORT,
-                    "in-kernel watchdog fired: wait site %u, block %u, thread %u, parity %u",
+                    "in-kernel watchdog fired: wait site %u, block %u, thread %u, blocked-site mask 0x%x",
                     h[0] & 0x7fffffffu, h[1], h[2], h[3]);
     return FA_SM100_OK;
 }
@@ -347,4 +496,9 @@ extern "C" int fa_sm100_internal_encode_2d(CUtensorMap* map, int is_bf16, const 
                       2, base, dims, strides, box, "selftest");
 }
 extern "C" void fa_sm100_internal_count_launch(void) { g_launches.fetch_add(1); }
+// Debug: device buffer of 5 x 4096 int64 that CTA 0 fills with (event << 56 | clock64) records;
+// only honoured by FA_SM100_TUNE builds (D=128 bf16 / D=64 fp16).  NULL switches tracing off.
+extern "C" void fa_sm100_internal_set_trace(void* device_buffer) {
+    g_trace = static_cast<long long*>(device_buffer);
+}
 extern "C" int fa_sm100_internal_fail(int code, const char* msg) { return fail(code, "%s", msg); }

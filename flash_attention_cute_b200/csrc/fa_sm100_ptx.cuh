@@ -91,15 +91,18 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, unsigne
     uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity)) {
         if ((++spins & 0x3ffu) == 0) {
-            if (*reinterpret_cast<volatile unsigned int*>(status) != 0u) return;  // someone aborted
+            if (*reinterpret_cast<volatile unsigned int*>(status) != 0u) {  // someone aborted
+                atomicOr(status + 3, 1u << (code & 31u));  // leave a trace of every blocked wait site
+                return;
+            }
             uint64_t now = global_timer_ns();
             if (t0 == 0) t0 = now;
             else if (now - t0 > kWatchdogNs) {
                 if (atomicCAS(status, 0u, 0x80000000u | code) == 0u) {
                     status[1] = blockIdx.x;
                     status[2] = threadIdx.x;
-                    status[3] = parity;
                 }
+                atomicOr(status + 3, 1u << (code & 31u));
                 return;
             }
         }
@@ -258,6 +261,95 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* r) {
         "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]),
         "r"(r[14]), "r"(r[15])
         : "memory");
+}
+
+// ----------------------------------------------------------------------------------------------
+// packed fp32x2 arithmetic (sm_100: FFMA2 / FADD2) and the FMA-pipe exp2
+// ----------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t pack_f32x2(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack_f32x2(uint64_t v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma_f32x2(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t d;
+    asm("fma.rn.ftz.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ uint64_t add_f32x2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("add.rn.ftz.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ uint64_t sub_f32x2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("sub.rn.ftz.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ uint64_t add_rm_f32x2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("add.rm.ftz.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ float max3(float a, float b, float c) {
+    float d;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+
+// 2^x for x <= 0 on the FMA/ALU pipes (no MUFU): Cody–Waite split x = floor(x) + f, f in [0,1),
+// 2^f by a degree-3 minimax polynomial with p(0) = 1 (max relative error 8.6e-5, well under the
+// 2^-9 / 2^-11 rounding of P to bf16 / fp16), exponent added in the integer domain.  The softmax
+// warps use it for a fraction of the elements so that MUFU.EX2 (16/clk/SM) stops being the
+// co-critical pipe next to the tensor core.  Inputs below -127 (masked scores) clamp to ~2^-127.
+__device__ __forceinline__ void ex2_emu_x2(uint64_t x, float& out_lo, float& out_hi) {
+    float x0, x1;
+    unpack_f32x2(x, x0, x1);
+    x0 = fmaxf(x0, -127.f);
+    x1 = fmaxf(x1, -127.f);
+    const uint64_t xc = pack_f32x2(x0, x1);
+    const uint64_t magic = pack_f32x2(12582912.f, 12582912.f);  // 1.5 * 2^23
+    const uint64_t fl = add_rm_f32x2(xc, magic);                 // low mantissa bits = floor(x)
+    const uint64_t fr = sub_f32x2(xc, sub_f32x2(fl, magic));     // f = x - floor(x)
+    uint64_t p = fma_f32x2(fr, pack_f32x2(0.07706704f, 0.07706704f), pack_f32x2(0.22764499f, 0.22764499f));
+    p = fma_f32x2(p, fr, pack_f32x2(0.69511676f, 0.69511676f));
+    p = fma_f32x2(p, fr, pack_f32x2(1.f, 1.f));
+    float p0, p1, f0, f1;
+    unpack_f32x2(p, p0, p1);
+    unpack_f32x2(fl, f0, f1);
+    out_lo = __uint_as_float(__float_as_uint(p0) + (__float_as_uint(f0) << 23));
+    out_hi = __uint_as_float(__float_as_uint(p1) + (__float_as_uint(f1) << 23));
+}
+
+// Scalar form of the same emulation with immediate operands (FADD/FFMA with an immediate issue
+// in one cycle on sm_100; the packed f32x2 forms take two), ~8 issue cycles per element.
+__device__ __forceinline__ float ex2_emu(float x) {
+    x = fmaxf(x, -127.f);
+    float fl, r, fr, q;
+    asm("add.rm.ftz.f32 %0, %1, 0f4B400000;" : "=f"(fl) : "f"(x));   // + 1.5 * 2^23, round down
+    asm("add.rn.ftz.f32 %0, %1, 0fCB400000;" : "=f"(r) : "f"(fl));   // floor(x)
+    asm("sub.rn.ftz.f32 %0, %1, %2;" : "=f"(fr) : "f"(x), "f"(r));   // f = x - floor(x)
+    asm("fma.rn.ftz.f32 %0, %1, 0f3D9DD553, 0f3E691BC5;" : "=f"(q) : "f"(fr));  // c3 f + c2
+    asm("fma.rn.ftz.f32 %0, %0, %1, 0f3F31F32C;" : "+f"(q) : "f"(fr));          // .. f + c1
+    asm("fma.rn.ftz.f32 %0, %0, %1, 0f3F800000;" : "+f"(q) : "f"(fr));          // .. f + 1
+    return __uint_as_float(__float_as_uint(q) + (__float_as_uint(fl) << 23));
+}
+
+__device__ __forceinline__ void st_shared_f32(uint32_t addr, float v) {
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ float ld_shared_f32(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ long long clock64_now() {
+    long long t;
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(t));
+    return t;
 }
 
 // ----------------------------------------------------------------------------------------------

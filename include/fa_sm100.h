@@ -56,6 +56,14 @@ enum fa_sm100_status {
 /* Flags for fa_sm100_fwd_params.flags */
 #define FA_SM100_FLAG_NO_PACK_GQA 1u   /* do not pack the q heads of a kv group into one M tile */
 #define FA_SM100_FLAG_FORCE_PACK_GQA 2u /* pack whenever Hq/Hkv > 1 (default: heuristic)        */
+#define FA_SM100_FLAG_KERNEL_V1 4u      /* debug: first-generation (non-persistent) kernel       */
+/* Tuning bits (honoured by FA_SM100_TUNE builds, ignored otherwise):
+ *   bits 8-11  1 + number of exp2 evaluations per 4 element pairs moved to the FMA pipe (0 = default)
+ *   bits 12-13 P hand-off split: 0 = default, 1 = 64 keys first, 2 = 96, 3 = no split
+ *   bits 14-15 softmax threads per query row: 0 = default, 1 or 2                                 */
+#define FA_SM100_FLAG_TUNE_EMU(n) ((uint32_t)((n) + 1) << 8)
+#define FA_SM100_FLAG_TUNE_SPLIT(sel) ((uint32_t)(sel) << 12)
+#define FA_SM100_FLAG_TUNE_HALVES(n) ((uint32_t)(n) << 14)
 
 typedef struct fa_sm100_fwd_params {
     const void* q;      /* device pointers, 16-byte aligned */
