@@ -16,7 +16,7 @@
 #include "../../include/fa_sm100.h"
 #include "fa_sm100_kernel.cuh"
 #include "fa_sm100_fwd.cuh"
-#include "fa_sm100_fwd3.cuh"
+#include "fa_sm100_fwd4.cuh"
 
 namespace {
 
@@ -147,37 +147,38 @@ Variant2* pick_tuned(int halves, int emu, int split, bool trace) {
     if (halves == H && emu == E && split == S)                                                   \
         return trace ? variant2<kD, kBf16, stages_for<kD, H>(), E, S, H, true>()                 \
                      : variant2<kD, kBf16, stages_for<kD, H>(), E, S, H, false>();
-    FA_V(1, 0, 64) FA_V(1, 1, 64) FA_V(1, 2, 64)
-    FA_V(1, 0, 128) FA_V(1, 1, 128) FA_V(1, 2, 128)
-    FA_V(2, 0, 128) FA_V(2, 1, 128) FA_V(2, 2, 128)
+    FA_V(1, 0, 128) FA_V(2, 0, 128)
 #undef FA_V
 #endif
     (void)halves; (void)emu; (void)split; (void)trace;
     return nullptr;
 }
 
-// ---- generation-3 kernel variants (fa_sm100_fwd3.cuh): one M-tile per CTA ----
-template <int kD, bool kBf16, int kEmu, bool kTrace>
-Variant2* variant3() {
-    constexpr int kStages = kD == 64 ? 12 : 5;
-    static Variant2 v{fa100::v3::fa_fwd_sm100_v3<kD, kBf16, kStages, kEmu, kTrace>,
-                      fa100::v3::Smem<kD, kStages>::kDynamicBytes, fa100::v3::kNumThreads};
+// ---- generation-4 kernel variants (fa_sm100_fwd4.cuh) ----
+template <int kD, bool kBf16, int kEmu, int kSplit, bool kTrace>
+Variant2* variant4() {
+    constexpr int kStages = kD == 64 ? 8 : 5;
+    static Variant2 v{fa100::v4::fa_fwd_sm100_v4<kD, kBf16, kStages, kEmu, kSplit, kTrace>,
+                      fa100::v4::Smem<kD, kStages>::kDynamicBytes, fa100::v4::Cfg::kNumThreads};
     return &v;
 }
-constexpr int kDefEmu3 = 0;
-Variant2* pick_variant3(int kd, bool bf16, int emu, bool trace) {
-    if (emu < 0) emu = kDefEmu3;
+constexpr int kDefEmu4 = 0, kDefSplit4 = 128;
+Variant2* pick_variant4(int kd, bool bf16, int emu, int split, bool trace) {
+    if (emu < 0) emu = kDefEmu4;
+    if (split < 0) split = kDefSplit4;
 #ifdef FA_SM100_TUNE
-#define FA_V3(D, BF, E)                                                                    \
-    if (kd == D && bf16 == BF && emu == E)                                                 \
-        return trace ? variant3<D, BF, E, true>() : variant3<D, BF, E, false>();
-    FA_V3(128, true, 0) FA_V3(128, true, 1) FA_V3(128, true, 2)
-    FA_V3(64, false, 0) FA_V3(64, false, 1) FA_V3(64, false, 2)
-#undef FA_V3
+#define FA_V4(D, BF, E, S)                                                                 \
+    if (kd == D && bf16 == BF && emu == E && split == S)                                   \
+        return trace ? variant4<D, BF, E, S, true>() : variant4<D, BF, E, S, false>();
+    FA_V4(128, true, 0, 128) FA_V4(128, true, 1, 128) FA_V4(128, true, 2, 128) FA_V4(128, true, 3, 128)
+    FA_V4(128, true, 0, 96) FA_V4(128, true, 1, 96) FA_V4(128, true, 2, 96) FA_V4(128, true, 3, 96)
+    FA_V4(128, true, 0, 64) FA_V4(128, true, 2, 64)
+#undef FA_V4
 #endif
     (void)trace;
-    if (kd == 128) return bf16 ? variant3<128, true, kDefEmu3, false>() : variant3<128, false, kDefEmu3, false>();
-    return bf16 ? variant3<64, true, kDefEmu3, false>() : variant3<64, false, kDefEmu3, false>();
+    constexpr int E = kDefEmu4, S = kDefSplit4;
+    if (kd == 128) return bf16 ? variant4<128, true, E, S, false>() : variant4<128, false, E, S, false>();
+    return bf16 ? variant4<64, true, E, S, false>() : variant4<64, false, E, S, false>();
 }
 
 Variant2* pick_variant2(int kd, bool bf16, int halves, int emu, int split, bool trace) {
@@ -196,13 +197,13 @@ Variant2* pick_variant2(int kd, bool bf16, int halves, int emu, int split, bool 
                 : variant2<64, false, stages_for<64, H>(), E, S, H, false>();
 }
 
-constexpr bool kDefaultGen3Static = false;  // which generation fa_sm100_fwd launches by default
-// FA_SM100_GEN=2|3 in the environment overrides the default generation (test / tuning aid).
-const bool kDefaultGen3 = [] {
+constexpr bool kDefaultGen4Static = true;  // true: generation 4 (fa_sm100_fwd4.cuh) is what fa_sm100_fwd launches
+// FA_SM100_GEN=2|4 in the environment overrides the default generation (test / tuning aid).
+const bool kDefaultGen4 = [] {
     const char* e = getenv("FA_SM100_GEN");
-    if (e && e[0] == '3') return true;
+    if (e && e[0] == '4') return true;
     if (e && e[0] == '2') return false;
-    return kDefaultGen3Static;
+    return kDefaultGen4Static;
 }();
 long long* g_trace = nullptr;  // debug timeline buffer (fa_sm100_internal_set_trace)
 
@@ -342,9 +343,9 @@ extern "C" int fa_sm100_fwd(const fa_sm100_fwd_params* p, void* stream) {
     const int tune_split = kSplitSel[(p->flags >> 12) & 0x3u];
     Variant* var = plan.var;
     const int tune_halves = int((p->flags >> 14) & 0x3u) == 0 ? -1 : int((p->flags >> 14) & 0x3u);
-    const bool use_v3 = !use_v1 && (tune_halves == 3 || (tune_halves < 0 && kDefaultGen3));
+    const bool use_v4 = !use_v1 && (tune_halves == 3 || (tune_halves < 0 && kDefaultGen4));
     Variant2* var2 = use_v1 ? nullptr
-                   : use_v3 ? pick_variant3(plan.kd, p->dtype == FA_SM100_BF16, tune_emu, g_trace != nullptr)
+                   : use_v4 ? pick_variant4(plan.kd, p->dtype == FA_SM100_BF16, tune_emu, tune_split, g_trace != nullptr)
                             : pick_variant2(plan.kd, p->dtype == FA_SM100_BF16, tune_halves, tune_emu,
                                             tune_split, g_trace != nullptr);
     const int smem_bytes = use_v1 ? var->smem_bytes : var2->smem_bytes;
@@ -414,7 +415,7 @@ extern "C" int fa_sm100_fwd(const fa_sm100_fwd_params* p, void* stream) {
     kp.headdim = int(p->headdim);
     kp.pack_g = plan.pack_g;
     kp.rows_per_head = plan.rows_per_head;
-    kp.num_m_blocks = use_v3 ? int((p->seqlen_q + plan.rows_per_head - 1) / plan.rows_per_head) : plan.num_m_blocks;
+    kp.num_m_blocks = plan.num_m_blocks;
     kp.head_units = plan.head_units;
     kp.total_heads = plan.head_units * int(p->batch);
     kp.num_tiles = kp.num_m_blocks * kp.total_heads;

@@ -78,6 +78,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
     return ok != 0;
 }
 
+// Non-blocking probe of a phase (the MMA issuer polls several barriers round-robin).
+__device__ __forceinline__ bool mbar_test_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+
 // Bounded wait.  A protocol bug in a warp-specialised kernel otherwise hangs the GPU; here every
 // wait gives up after kWatchdogNs, records (code, bar, parity) in the status words and raises the
 // abort flag, after which all waits in the grid fall through so the kernel terminates normally
