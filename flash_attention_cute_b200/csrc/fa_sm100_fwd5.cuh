@@ -1,0 +1,570 @@
+// FlashAttention-2 forward for sm_100a, generation 5: half-block software pipeline.
+//
+// Replaces the reference's flash_attention_v2 (csrc/flash_attention_template.cuh:138-564),
+// Mask (csrc/mask.cuh:30-88) and launch_flash_attention (template.cuh:567-583).  Same math
+// (fp32 S and O accumulators, exp2-domain online softmax, P rounded to T before P·V, row sums
+// from unrounded P, bottom-right causal alignment, kv-head = q-head / G).
+//
+// What generations 1-4 taught (profiles/r01): with one 128-column S buffer per M-tile the
+// dependency chain  S(j) -> softmax -> P(j) -> P·V(j) -> S(j+1)  is serial per tile, a lone
+// softmax warp gets ~10 cycles per exp2 out of its SM sub-partition's MUFU, and the period per
+// KV block comes out near 3500 cycles against 2048 cycles of tensor work: both the tensor pipe
+// and the MUFU idle ~45 % of the time.  TMEM (512 columns = 2 x 128 S + 2 x 128 O) has no room
+// for a second 128-column S buffer, so this kernel cuts every KV block in two 64-key halves:
+//
+//   TMEM: tile t, buffer b: S/P at columns [128 t + 64 b, +64); O_t at [256 + D t, +D).
+//   per tile the half-blocks h = 0, 1, 2, ... alternate between the two buffers, so that
+//   S(h+1) is already waiting when softmax(h) ends and S(h+2) is issued right behind P·V(h):
+//   the softmax warpgroups run back to back and the tensor pipe always has the other buffer's
+//   or the other tile's MMAs queued.  The price is N = 64 for Q·Kᵀ (shared-memory bound,
+//   48 instead of 32 cycles per K=16 step); P·V keeps N = D.
+//
+//   grid = min(#SMs, #work tiles) persistent CTAs of 512 threads; work tile = 2 M-tiles of 128
+//   query rows sharing one K/V stream; LPT + L2-section order, dynamic scheduler (as gen 2-4).
+//     warps 0-3   softmax warpgroup, M-tile 0 (one thread per query row, no shuffles); also
+//                 performs the (rare) lazy rescale of O_t in TMEM
+//     warps 4-7   softmax warpgroup, M-tile 1
+//     warps 8-11  epilogue warpgroup: O_t / l -> T -> global, whichever tile finishes first
+//     warps 12,13 MMA issuers (one elected thread each), one per M-tile: S_t = Q_t·Khᵀ (SS),
+//                 O_t += P_t·Vh (TS).  A K/V slot is released when both have committed on it.
+//     warp  14    TMA producer (one elected thread)
+//     warp  15    spare (registers go to the softmax warpgroups via setmaxnreg)
+#pragma once
+#include "fa_sm100_fwd4.cuh"
+
+namespace fa100 {
+namespace v5 {
+
+using v4::Tile;
+using v4::decode_tile;
+using v4::TileConsumer;
+using v4::Tracer;
+using v4::kSchedDepth;
+using v4::kPanelBytes;
+using v4::kBlockN;
+using v4::kRescaleThreshold;
+
+struct Cfg {
+    static constexpr int kSoftmaxWarps = 8;
+    static constexpr int kEpiWarp0 = 8;
+    static constexpr int kMmaWarp = 12;   // 12: M-tile 0, 13: M-tile 1
+    static constexpr int kLoadWarp = 14;
+    static constexpr int kNumWarps = 16;
+    static constexpr int kNumThreads = kNumWarps * 32;
+    static constexpr int kRegsLaunch = 128;  // 64K / 512
+    static constexpr int kRegsSoftmax = 168;
+    static constexpr int kRegsEpi = 112;
+    static constexpr int kRegsOther = 64;
+    static_assert(kSoftmaxWarps * kRegsSoftmax + 4 * kRegsEpi + 4 * kRegsOther <= kNumWarps * kRegsLaunch,
+                  "register budget");
+};
+
+template <int kD, int kStages>
+struct Smem {
+    static constexpr int kPanels = kD / 64;
+    static constexpr int kTileBytes = kPanels * kPanelBytes;  // a Q M-tile or one K / V block
+    static constexpr int kQ0 = 0;
+    static constexpr int kQ1 = kTileBytes;
+    static constexpr int kKV = 2 * kTileBytes;
+    static constexpr int kHalfBytes = kTileBytes / 2;           // 64 keys of K or V
+    static constexpr int kHalfPanel = kPanelBytes / 2;          // 64 rows x 64 16-bit elements
+    static constexpr int kRowSum = kKV + kStages * kHalfBytes;  // float [2][128] final row sums
+    static constexpr int kTileRing = kRowSum + 2 * 128 * 4;      // int [kSchedDepth]
+    static constexpr int kBars = kTileRing + 16;
+    // barrier slots (8 B each)
+    static constexpr int kBarQFull = 0;                  // [2]     TMA -> MMA
+    static constexpr int kBarQEmpty = 2;                 // [2]     MMA commit -> TMA
+    static constexpr int kBarKVFull = 4;                 // [kStages]
+    static constexpr int kBarKVEmpty = 4 + kStages;      // [kStages]
+    static constexpr int kBarSFull = 4 + 2 * kStages;    // [2][2]  MMA commit -> softmax   (tile, buffer)
+    static constexpr int kBarPFull = 8 + 2 * kStages;    // [2][2]  softmax (4 warps) -> MMA (tile, buffer)
+    static constexpr int kBarPVDone = 12 + 2 * kStages;  // [2]     MMA commit after every P·V (rescale guard)
+    static constexpr int kBarRowSum = 14 + 2 * kStages;  // [2]     softmax (4 warps) -> epilogue
+    static constexpr int kBarOFull = 16 + 2 * kStages;   // [2]     MMA commit -> epilogue
+    static constexpr int kBarOEmpty = 18 + 2 * kStages;  // [2]     epilogue (4 warps) -> MMA
+    static constexpr int kBarTileFull = 20 + 2 * kStages;   // [kSchedDepth] producer -> everyone
+    static constexpr int kBarTileEmpty = 24 + 2 * kStages;  // [kSchedDepth] consumer warps -> producer
+    static constexpr int kNumBars = 28 + 2 * kStages;
+    static constexpr int kTmemPtr = kBars + kNumBars * 8;
+    static constexpr int kTotal = kTmemPtr + 16;
+    static constexpr int kDynamicBytes = kTotal;
+};
+
+
+// kEmu: of every 8 element pairs, how many take the FMA-pipe exp2 (0 = all MUFU).
+template <int kD, bool kBf16, int kStages, int kEmu, bool kTrace>
+__global__ void __launch_bounds__(Cfg::kNumThreads, 1)
+fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
+    using L = Smem<kD, kStages>;
+    using C = Cfg;
+    constexpr int kEpiWarp0 = C::kEpiWarp0, kMmaWarp = C::kMmaWarp, kLoadWarp = C::kLoadWarp;
+    constexpr int kPanels = L::kPanels;
+    constexpr uint32_t kHalfBytes = L::kHalfBytes;
+    constexpr uint32_t kHalfPanel = L::kHalfPanel;
+    // tcgen05.fence::after_thread_sync in front of every MMA batch: measured to drain the tensor pipe
+    // (the next batch is only accepted once the previous one has executed), which halves the issue
+    // rate.  P reaches TMEM through tcgen05.st + tcgen05.wait::st before the softmax warps arrive on
+    // PFull, K/V through TMA complete_tx, so the mbarrier acquire is what orders the MMAs here.
+    constexpr bool kFenceMma = false;
+
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    const uint32_t smem_base = smem_u32(smem_raw);
+    uint8_t* smem_gen = smem_raw;
+    if (smem_base & 1023u) {  // 128B-swizzled TMA/UMMA tiles need a 1024 B aligned base
+        if (threadIdx.x == 0) atomicCAS(params.status, 0u, 0x80000063u);
+        return;
+    }
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    unsigned int* status = params.status;
+    auto bar = [&](int slot) -> uint32_t { return smem_base + L::kBars + slot * 8; };
+
+    // ---- one-time setup ----
+    if (warp == kLoadWarp && lane == 0) {
+        prefetch_tensormap(&params.tm_q);
+        prefetch_tensormap(&params.tm_k);
+        prefetch_tensormap(&params.tm_v);
+        for (int t = 0; t < 2; ++t) {
+            mbar_init(bar(L::kBarQFull + t), 1);
+            mbar_init(bar(L::kBarQEmpty + t), 1);
+            for (int b = 0; b < 2; ++b) {
+                mbar_init(bar(L::kBarSFull + 2 * t + b), 1);
+                mbar_init(bar(L::kBarPFull + 2 * t + b), 4);
+            }
+            mbar_init(bar(L::kBarPVDone + t), 1);
+            mbar_init(bar(L::kBarRowSum + t), 4);
+            mbar_init(bar(L::kBarOFull + t), 1);
+            mbar_init(bar(L::kBarOEmpty + t), 4);
+        }
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(bar(L::kBarKVFull + s), 1);
+            mbar_init(bar(L::kBarKVEmpty + s), 2);  // one arrival per MMA issuer
+        }
+        for (int s = 0; s < kSchedDepth; ++s) {
+            mbar_init(bar(L::kBarTileFull + s), 1);
+            mbar_init(bar(L::kBarTileEmpty + s), C::kSoftmaxWarps + 4 + 2);  // softmax + epilogue + 2 MMA
+        }
+        fence_mbar_init();
+    }
+    if (warp == kMmaWarp) {
+        tmem_alloc(smem_base + L::kTmemPtr, 512);
+        tmem_relinquish_alloc_permit();
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_gen + L::kTmemPtr);
+    const int P = params.rows_per_head;
+    const bool packed = params.pack_g > 1;
+    Tracer<kTrace> tr;
+
+    if (warp >= kMmaWarp) {
+        reg_dealloc<C::kRegsOther>();
+        // elect_one() rather than lane == 0: ptxas then knows the role runs on one thread with uniform
+        // operands and emits back-to-back UTCHMMA / UTMALDG without a per-instruction elect loop.
+        const bool elected = elect_one();
+        if (warp == kLoadWarp && elected) {
+            // =========================== TMA producer ===========================
+            tr.init(params, 4, true);
+            int slot = 0;
+            uint32_t phase = 0;
+            uint32_t qe_phase[2] = {0, 0};
+            Tile w;
+            int next_idx = blockIdx.x;  // first tile: no atomic
+            for (int round = 0;; ++round) {
+                // publish this round's tile index (or the end marker) to the other warps
+                const int idx = next_idx < params.num_tiles ? next_idx : -1;
+                const int ts = round % kSchedDepth;
+                mbar_wait(bar(L::kBarTileEmpty + ts), ((round / kSchedDepth) & 1) ^ 1u, status, 21);
+                asm volatile("st.shared.s32 [%0], %1;" ::"r"(smem_base + L::kTileRing + ts * 4), "r"(idx) : "memory");
+                mbar_arrive(bar(L::kBarTileFull + ts));
+                if (idx < 0) break;
+                // prefetch the next index; the atomic's latency hides behind this tile's TMA issue
+                next_idx = int(gridDim.x) + atomicAdd(params.sched, 1);
+                decode_tile(params, idx, w);
+#pragma unroll
+                for (int t = 0; t < 2; ++t) {
+                    if (w.nblk[t] > 0) {
+                        mbar_wait(bar(L::kBarQEmpty + t), qe_phase[t] ^ 1u, status, 10);
+                        qe_phase[t] ^= 1u;
+                        const uint32_t qbar = bar(L::kBarQFull + t);
+                        mbar_arrive_expect_tx(qbar, params.q_tile_bytes);
+                        for (int pn = 0; pn < kPanels; ++pn)
+                            tma_load_5d(smem_base + (t ? L::kQ1 : L::kQ0) + pn * kPanelBytes,
+                                        &params.tm_q, qbar, pn * 64, w.pos0[t], w.g_coord, w.kv_head, w.b);
+                    }
+                }
+                tr.ev(1);
+                // 64-key half tiles in the order the MMA issuer consumes them:
+                //   K0 K1 | V0 K2 | V1 K3 | ... | V(nh-3) K(nh-1) | V(nh-2) | V(nh-1)
+                const int nh = 4 * w.nmax / 2;  // half-blocks of the longer M-tile
+                for (int it = 0; it < 2 * nh; ++it) {
+                    bool is_v;
+                    int h;
+                    if (it < 2) { is_v = false; h = it; }
+                    else if (it == 2 * nh - 1) { is_v = true; h = nh - 1; }
+                    else { const int rr = it - 2; is_v = (rr & 1) == 0; h = is_v ? (rr >> 1) : (rr >> 1) + 2; }
+                    const CUtensorMap* tm = is_v ? &params.tm_v : &params.tm_k;
+                    mbar_wait(bar(L::kBarKVEmpty + slot), phase ^ 1u, status, 1);
+                    const uint32_t fb = bar(L::kBarKVFull + slot);
+                    mbar_arrive_expect_tx(fb, kHalfBytes);
+                    for (int pn = 0; pn < kPanels; ++pn)
+                        tma_load_4d(smem_base + L::kKV + slot * kHalfBytes + pn * kHalfPanel, tm, fb,
+                                    pn * 64, h * 64, w.kv_head, w.b);
+                    if (++slot == kStages) { slot = 0; phase ^= 1u; }
+                }
+            }
+        } else if ((warp == kMmaWarp || warp == kMmaWarp + 1) && elected) {
+            // =========================== MMA issuer ===========================
+            tr.init(params, 3, warp == kMmaWarp);
+            constexpr uint32_t idesc_qk = make_idesc_f16(kBf16, 128, 64, false, false);
+            constexpr uint32_t idesc_pv = make_idesc_f16(kBf16, 128, kD, false, true);
+            // UMMA smem descriptors are rebuilt per instruction from a 32-bit base (start address
+            // field) plus a compile-time offset.
+            constexpr uint32_t kDescHi = (1024u >> 4) | (1u << 14) | (2u << 29);  // SBO, version, SW128
+            constexpr uint32_t kLboK = (16u >> 4) << 16;                          // Q, K: K-major panels
+            constexpr uint32_t kLboV = (kHalfPanel >> 4) << 16;                   // V: MN-major panels
+            auto desc = [](uint32_t lo) -> uint64_t {
+                uint64_t d;
+                asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(kDescHi));
+                return d;
+            };
+            const uint32_t q_lo0 = ((smem_base + L::kQ0) >> 4) | kLboK, q_lo1 = ((smem_base + L::kQ1) >> 4) | kLboK;
+            const uint32_t kv_lo = (smem_base + L::kKV) >> 4;  // + slot * (kHalfBytes >> 4)
+
+            // S(t, buffer b) = Q_t · Khᵀ, Kh = the 64-key half tile in ring slot kslot_
+            auto issue_s = [&](int t, int b, int kslot_) {
+                const uint32_t k_lo = (kv_lo + kslot_ * (kHalfBytes >> 4)) | kLboK;
+                const uint32_t d = tmem_base + t * 128 + b * 64;
+#pragma unroll
+                for (int ks = 0; ks < kD / 16; ++ks) {
+                    const uint32_t qoff = ((ks >> 2) * kPanelBytes + (ks & 3) * 32) >> 4;
+                    const uint32_t koff = ((ks >> 2) * kHalfPanel + (ks & 3) * 32) >> 4;
+                    umma_ss(d, desc((t ? q_lo1 : q_lo0) + qoff), desc(k_lo + koff), idesc_qk, ks > 0);
+                }
+            };
+            // O_t += P(t, buffer b) · Vh, Vh = the 64-key half tile in ring slot vslot_
+            auto issue_pv = [&](int t, int b, int vslot_, bool acc) {
+                const uint32_t v_lo = (kv_lo + vslot_ * (kHalfBytes >> 4)) | kLboV;
+                const uint32_t a = tmem_base + t * 128 + b * 64;
+                const uint32_t d = tmem_base + 256 + t * kD;
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks)
+                    umma_ts(d, a + ks * 8, desc(v_lo + ks * (2048 >> 4)), idesc_pv, (acc || ks > 0) ? 1u : 0u);
+            };
+
+            // Ring position of this work tile's first half tile (the producer's order is
+            // K0 K1 | V0 K2 | V1 K3 | ... | V(nh-2) | V(nh-1), nh = half-blocks of the longer M-tile).
+            const int t = warp - kMmaWarp;
+            int slot0 = 0;
+            uint32_t phase0 = 0;
+            uint32_t q_phase = 0, oe_phase = 0;
+            uint32_t blk_base = 0;  // KV blocks of earlier work tiles, mod 2 (P barrier parity)
+            Tile w;
+            TileConsumer<L> sched(smem_base, status);
+            while (sched.next(params, w, true)) {
+                if (w.nmax == 0) continue;
+                auto ring = [&](int it, int& s_, uint32_t& ph_) {
+                    const int x = slot0 + it;
+                    const int q = x / kStages;
+                    s_ = x - q * kStages;
+                    ph_ = phase0 ^ static_cast<uint32_t>(q & 1);
+                };
+                const int nh = 2 * w.nblk[t];
+                const int nhmax = 2 * w.nmax;
+                auto idx_k = [](int h) { return h < 2 ? h : 2 * h - 1; };
+                auto idx_v = [&](int h) { return h == nhmax - 1 ? 2 * nhmax - 1 : 2 + 2 * h; };
+                // wait for a half tile; returns its slot
+                auto acquire = [&](int it, uint32_t code) {
+                    int sl; uint32_t ph;
+                    ring(it, sl, ph);
+                    mbar_wait(bar(L::kBarKVFull + sl), ph, status, code);
+                    return sl;
+                };
+                if (nh > 0) {
+                    // prologue: S(0), S(1)
+                    mbar_wait(bar(L::kBarQFull + t), q_phase, status, 3);
+                    q_phase ^= 1u;
+#pragma unroll
+                    for (int hh = 0; hh < 2; ++hh) {
+                        const int ks = acquire(idx_k(hh), 2);
+                        issue_s(t, hh, ks);
+                        tc_commit(bar(L::kBarSFull + 2 * t + hh));
+                        tc_commit(bar(L::kBarKVEmpty + ks));
+                    }
+                    if (nh == 2) tc_commit(bar(L::kBarQEmpty + t));
+                    tr.ev(2);
+                    for (int h = 0; h < nh; ++h) {
+                        const int b = h & 1;
+                        mbar_wait(bar(L::kBarPFull + 2 * t + b), (blk_base + (h >> 1)) & 1u, status, 5);
+                        if (h == 0) {  // O_t of the previous work tile must have been drained
+                            mbar_wait(bar(L::kBarOEmpty + t), oe_phase ^ 1u, status, 11);
+                            oe_phase ^= 1u;
+                        }
+                        const int vs = acquire(idx_v(h), 4);
+                        if (kFenceMma) tc_fence_after_sync();
+                        tr.ev(3);
+                        issue_pv(t, b, vs, h > 0);
+                        tc_commit(bar(L::kBarPVDone + t));
+                        tc_commit(bar(L::kBarKVEmpty + vs));
+                        if (h + 2 < nh) {
+                            const int ks = acquire(idx_k(h + 2), 6);
+                            issue_s(t, b, ks);
+                            tc_commit(bar(L::kBarSFull + 2 * t + b));
+                            tc_commit(bar(L::kBarKVEmpty + ks));
+                            if (h + 3 == nh) tc_commit(bar(L::kBarQEmpty + t));
+                        }
+                        if (h + 1 == nh) tc_commit(bar(L::kBarOFull + t));
+                        tr.ev(5);
+                    }
+                }
+                // half tiles only the other (longer) M-tile uses: stay in lockstep with the ring
+                for (int h = nh; h < nhmax; ++h) {
+                    const int ks = acquire(idx_k(h), 16);
+                    mbar_arrive(bar(L::kBarKVEmpty + ks));
+                    const int vs = acquire(idx_v(h), 17);
+                    mbar_arrive(bar(L::kBarKVEmpty + vs));
+                }
+                blk_base += static_cast<uint32_t>(w.nblk[t]);
+                {
+                    const int x = slot0 + 4 * w.nmax;  // 2 nhmax half tiles
+                    const int q = x / kStages;
+                    slot0 = x - q * kStages;
+                    phase0 ^= static_cast<uint32_t>(q & 1);
+                }
+            }
+        }
+    } else if (warp >= kEpiWarp0) {
+        // =========================== epilogue warpgroup ===========================
+        reg_dealloc<C::kRegsEpi>();
+        tr.init(params, 2, warp == kEpiWarp0 && lane == 0);
+        const int r = threadIdx.x & 127;  // row inside an M-tile == TMEM lane
+        const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
+        uint32_t rs_phase[2] = {0, 0}, of_phase[2] = {0, 0};
+        Tile w;
+        TileConsumer<L> sched(smem_base, status);
+        while (sched.next(params, w, lane == 0)) {
+            // O / l -> T -> global (row-contiguous 16 B stores)
+#pragma unroll
+            for (int t = 0; t < 2; ++t) {
+                if (w.pos0[t] >= params.seqlen_q) continue;
+                const int n = w.nblk[t];
+                const int g = r / P;
+                const int pos = w.pos0[t] + (r - g * P);
+                const bool row_valid = (g < params.pack_g) && (pos < params.seqlen_q);
+                const int head = packed ? w.hu * params.group + g : w.hu;
+                uint8_t* orow = reinterpret_cast<uint8_t*>(params.o) +
+                                2 * (static_cast<int64_t>(w.b) * params.o_stride_b +
+                                     static_cast<int64_t>(head) * params.o_stride_h +
+                                     static_cast<int64_t>(pos) * params.o_stride_s);
+                float inv = 0.f;
+                if (n > 0) {
+                    mbar_wait(bar(L::kBarRowSum + t), rs_phase[t], status, 14);
+                    rs_phase[t] ^= 1u;
+                    const float l = ld_shared_f32(smem_base + L::kRowSum + (t * 128 + r) * 4);
+                    inv = (l > 0.f) ? __frcp_rn(l) : 0.f;
+                    mbar_wait(bar(L::kBarOFull + t), of_phase[t], status, 8);
+                    of_phase[t] ^= 1u;
+                    tc_fence_after_sync();
+                    tr.ev(8);
+                }
+                const uint32_t tmem_o = tmem_base + lane_base + 256 + t * kD;
+#pragma unroll
+                for (int c = 0; c < kD / 32; ++c) {
+                    uint32_t o[32];
+                    if (n > 0) {
+                        tmem_ld32(tmem_o + c * 32, o);
+                        tmem_wait_ld();
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) o[i] = 0u;
+                    }
+                    if (c == kD / 32 - 1 && n > 0) {  // O_t fully read: the next work tile may overwrite it
+                        tc_fence_before_sync();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(bar(L::kBarOEmpty + t));
+                    }
+                    if (row_valid) {
+#pragma unroll
+                        for (int q4 = 0; q4 < 4; ++q4) {
+                            const int col = c * 32 + q4 * 8;
+                            if (col < params.headdim) {
+                                uint4 v;
+                                v.x = pack2<kBf16>(__uint_as_float(o[q4 * 8 + 0]) * inv,
+                                                   __uint_as_float(o[q4 * 8 + 1]) * inv);
+                                v.y = pack2<kBf16>(__uint_as_float(o[q4 * 8 + 2]) * inv,
+                                                   __uint_as_float(o[q4 * 8 + 3]) * inv);
+                                v.z = pack2<kBf16>(__uint_as_float(o[q4 * 8 + 4]) * inv,
+                                                   __uint_as_float(o[q4 * 8 + 5]) * inv);
+                                v.w = pack2<kBf16>(__uint_as_float(o[q4 * 8 + 6]) * inv,
+                                                   __uint_as_float(o[q4 * 8 + 7]) * inv);
+                                *reinterpret_cast<uint4*>(orow + col * 2) = v;
+                            }
+                        }
+                    }
+                }
+                tr.ev(9);
+            }
+        }
+    } else {
+        // =========================== softmax warpgroups ===========================
+        reg_alloc<C::kRegsSoftmax>();
+        const int t = warp >> 2;          // M-tile handled by this warpgroup
+        tr.init(params, t, (warp & 3) == 0 && lane == 0);
+        const int r = threadIdx.x & 127;  // query row inside the M-tile == TMEM lane
+        const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
+        const uint32_t tmem_s = tmem_base + lane_base + t * 128;
+        const uint32_t tmem_o = tmem_base + lane_base + 256 + t * kD;
+        const float scale_log2 = params.scale_log2;
+        const int causal_off = params.seqlen_k - params.seqlen_q;
+        const uint32_t rowsum_addr = smem_base + L::kRowSum + (t * 128 + r) * 4;
+        const uint64_t sc2 = pack_f32x2(scale_log2, scale_log2);
+        uint32_t blk_base = 0;  // KV blocks of earlier work tiles, mod 2 (S barrier parity)
+        Tile w;
+        TileConsumer<L> sched(smem_base, status);
+        while (sched.next(params, w, lane == 0)) {
+            const int n = w.nblk[t];
+            if (n == 0) continue;
+            const int my_pos0 = w.pos0[t];
+            const int g = r / P;
+            const int pos = my_pos0 + (r - g * P);
+            int row_limit = params.seqlen_k - 1;  // last visible column
+            if (params.causal) row_limit = min(row_limit, pos + causal_off);
+
+            float m = -INFINITY;  // running row max (raw score units), possibly stale (lazy rescale)
+            float l = 0.f;        // running row sum of exp2, relative to m
+            float msc = 0.f;      // m * scale_log2 (0 while m == -inf)
+            uint64_t nm2 = pack_f32x2(0.f, 0.f);  // (-msc, -msc)
+
+            for (int h = 0; h < 2 * n; ++h) {
+                const int b = h & 1;
+                mbar_wait(bar(L::kBarSFull + 2 * t + b), (blk_base + (h >> 1)) & 1u, status, 7);
+                tc_fence_after_sync();
+                tr.ev(1);
+
+                uint32_t s[64];
+                tmem_ld32(tmem_s + b * 64, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
+                tmem_ld32(tmem_s + b * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&s[32]));
+                tmem_wait_ld();
+                tr.ev(2);
+
+                // element mask only on half-blocks that cross the diagonal or the end of K
+                const int col0 = h * 64;
+                const bool need_mask = (col0 + 64 > params.seqlen_k) ||
+                                       (params.causal && (col0 + 63 > my_pos0 + causal_off));
+                if (need_mask) {
+                    const int rel = row_limit - col0;
+#pragma unroll
+                    for (int i = 0; i < 64; ++i)
+                        if (i > rel) s[i] = 0xff800000u;  // -inf
+                }
+
+                float mx0 = max3(__uint_as_float(s[0]), __uint_as_float(s[1]), __uint_as_float(s[2]));
+                float mx1 = max3(__uint_as_float(s[3]), __uint_as_float(s[4]), __uint_as_float(s[5]));
+                float mx2 = max3(__uint_as_float(s[6]), __uint_as_float(s[7]), __uint_as_float(s[8]));
+                float mx3 = max3(__uint_as_float(s[9]), __uint_as_float(s[10]), __uint_as_float(s[11]));
+#pragma unroll
+                for (int i = 12; i < 60; i += 8) {
+                    mx0 = max3(mx0, __uint_as_float(s[i]), __uint_as_float(s[i + 1]));
+                    mx1 = max3(mx1, __uint_as_float(s[i + 2]), __uint_as_float(s[i + 3]));
+                    mx2 = max3(mx2, __uint_as_float(s[i + 4]), __uint_as_float(s[i + 5]));
+                    mx3 = max3(mx3, __uint_as_float(s[i + 6]), __uint_as_float(s[i + 7]));
+                }
+                mx0 = max3(mx0, __uint_as_float(s[60]), __uint_as_float(s[61]));
+                mx1 = max3(mx1, __uint_as_float(s[62]), __uint_as_float(s[63]));
+                const float m_new = fmaxf(max3(m, mx0, mx1), fmaxf(mx2, mx3));
+
+                // lazy rescale: keep the stale max unless this row grew by more than 2^8
+                const bool grow = (m_new - m) * scale_log2 > kRescaleThreshold;  // false for NaN (-inf - -inf)
+                if (__any_sync(0xffffffffu, grow)) {
+                    float alpha = 1.f;
+                    if (grow) {
+                        alpha = ex2_approx((m - m_new) * scale_log2);
+                        m = m_new;
+                        msc = m * scale_log2;
+                        nm2 = pack_f32x2(-msc, -msc);
+                        l *= alpha;
+                    }
+                    if (h > 0) {
+                        // O_t must be quiescent: P·V(h-1) complete (P·V(h) cannot have been issued,
+                        // P(h) is not published yet).  One PVDone phase per half-block.
+                        tr.ev(7);
+                        mbar_wait(bar(L::kBarPVDone + t), (h - 1) & 1u, status, 15);
+                        tc_fence_after_sync();
+#pragma unroll
+                        for (int c = 0; c < kD / 32; ++c) {
+                            uint32_t o[32];
+                            tmem_ld32(tmem_o + c * 32, o);
+                            tmem_wait_ld();
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                                o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+                            tmem_st32(tmem_o + c * 32, o);
+                        }
+                        tmem_wait_st();
+                    }
+                }
+                tr.ev(3);
+
+                // exp2 of 64 keys -> 32 packed columns of P, stored straight back over S
+                uint64_t la = pack_f32x2(0.f, 0.f), lb = pack_f32x2(0.f, 0.f);
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    uint32_t pk[16];
+#pragma unroll
+                    for (int q = 0; q < 16; ++q) {
+                        const uint64_t x2 = fma_f32x2(
+                            pack_f32x2(__uint_as_float(s[c * 32 + 2 * q]), __uint_as_float(s[c * 32 + 2 * q + 1])),
+                            sc2, nm2);
+                        float p0, p1;
+                        if (((q * kEmu) & 7) < kEmu) {
+                            ex2_emu_x2(x2, p0, p1);
+                        } else {
+                            float x0, x1;
+                            unpack_f32x2(x2, x0, x1);
+                            p0 = ex2_approx(x0);
+                            p1 = ex2_approx(x1);
+                        }
+                        if (q & 1) lb = add_f32x2(lb, pack_f32x2(p0, p1));
+                        else la = add_f32x2(la, pack_f32x2(p0, p1));
+                        pk[q] = pack2<kBf16>(p0, p1);
+                    }
+                    tmem_st16(tmem_s + b * 64 + c * 16, pk);
+                }
+                tmem_wait_st();
+                tc_fence_before_sync();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar(L::kBarPFull + 2 * t + b));
+                tr.ev(4);
+                float l0, l1;
+                unpack_f32x2(add_f32x2(la, lb), l0, l1);
+                l += l0 + l1;
+            }
+            blk_base += static_cast<uint32_t>(n);
+            st_shared_f32(rowsum_addr, l);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(L::kBarRowSum + t));
+        }
+    }
+
+    // ---- teardown ----
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == kMmaWarp) {
+        tc_fence_after_sync();
+        tmem_dealloc(tmem_base, 512);
+    }
+    if (threadIdx.x == 0) {
+        // the last CTA out re-arms the scheduler for the next launch that uses this slot
+        __threadfence();
+        if (atomicAdd(params.sched + 1, 1) == int(gridDim.x) - 1) {
+            params.sched[0] = 0;
+            params.sched[1] = 0;
+            __threadfence();
+        }
+    }
+}
+
+}  // namespace v5
+}  // namespace fa100

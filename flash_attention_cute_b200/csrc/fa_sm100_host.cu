@@ -17,6 +17,7 @@
 #include "fa_sm100_kernel.cuh"
 #include "fa_sm100_fwd.cuh"
 #include "fa_sm100_fwd4.cuh"
+#include "fa_sm100_fwd5.cuh"
 
 namespace {
 
@@ -181,6 +182,31 @@ Variant2* pick_variant4(int kd, bool bf16, int emu, int split, bool trace) {
     return bf16 ? variant4<64, true, E, S, false>() : variant4<64, false, E, S, false>();
 }
 
+// ---- generation-5 kernel variants (fa_sm100_fwd5.cuh): half-block pipeline ----
+template <int kD, bool kBf16, int kEmu, bool kTrace>
+Variant2* variant5() {
+    constexpr int kStages = kD == 64 ? 16 : 10;  // 64-key half tiles of K / V
+    static Variant2 v{fa100::v5::fa_fwd_sm100_v5<kD, kBf16, kStages, kEmu, kTrace>,
+                      fa100::v5::Smem<kD, kStages>::kDynamicBytes, fa100::v5::Cfg::kNumThreads};
+    return &v;
+}
+constexpr int kDefEmu5 = 2;
+Variant2* pick_variant5(int kd, bool bf16, int emu, bool trace) {
+    if (emu < 0) emu = kDefEmu5;
+#ifdef FA_SM100_TUNE
+#define FA_V5(D, BF, E)                                                                    \
+    if (kd == D && bf16 == BF && emu == E)                                                 \
+        return trace ? variant5<D, BF, E, true>() : variant5<D, BF, E, false>();
+    FA_V5(128, true, 0) FA_V5(128, true, 1) FA_V5(128, true, 2) FA_V5(128, true, 3) FA_V5(128, true, 4)
+    FA_V5(64, false, 0) FA_V5(64, false, 1) FA_V5(64, false, 2) FA_V5(64, false, 3)
+#undef FA_V5
+#endif
+    (void)trace;
+    constexpr int E = kDefEmu5;
+    if (kd == 128) return bf16 ? variant5<128, true, E, false>() : variant5<128, false, E, false>();
+    return bf16 ? variant5<64, true, E, false>() : variant5<64, false, E, false>();
+}
+
 Variant2* pick_variant2(int kd, bool bf16, int halves, int emu, int split, bool trace) {
     if (halves < 0) halves = kDefHalves;
     if (emu < 0) emu = kDefEmu;
@@ -197,13 +223,12 @@ Variant2* pick_variant2(int kd, bool bf16, int halves, int emu, int split, bool 
                 : variant2<64, false, stages_for<64, H>(), E, S, H, false>();
 }
 
-constexpr bool kDefaultGen4Static = true;  // true: generation 4 (fa_sm100_fwd4.cuh) is what fa_sm100_fwd launches
+constexpr int kDefaultGenStatic = 5;  // true: generation 4 (fa_sm100_fwd4.cuh) is what fa_sm100_fwd launches
 // FA_SM100_GEN=2|4 in the environment overrides the default generation (test / tuning aid).
-const bool kDefaultGen4 = [] {
+const int kDefaultGen = [] {
     const char* e = getenv("FA_SM100_GEN");
-    if (e && e[0] == '4') return true;
-    if (e && e[0] == '2') return false;
-    return kDefaultGen4Static;
+    if (e && (e[0] == '2' || e[0] == '4' || e[0] == '5')) return e[0] - '0';
+    return kDefaultGenStatic;
 }();
 long long* g_trace = nullptr;  // debug timeline buffer (fa_sm100_internal_set_trace)
 
@@ -343,8 +368,10 @@ extern "C" int fa_sm100_fwd(const fa_sm100_fwd_params* p, void* stream) {
     const int tune_split = kSplitSel[(p->flags >> 12) & 0x3u];
     Variant* var = plan.var;
     const int tune_halves = int((p->flags >> 14) & 0x3u) == 0 ? -1 : int((p->flags >> 14) & 0x3u);
-    const bool use_v4 = !use_v1 && (tune_halves == 3 || (tune_halves < 0 && kDefaultGen4));
+    const bool use_v4 = !use_v1 && tune_halves == 3;
+    const bool use_v5 = !use_v1 && tune_halves < 0 && kDefaultGen == 5;
     Variant2* var2 = use_v1 ? nullptr
+                   : use_v5 ? pick_variant5(plan.kd, p->dtype == FA_SM100_BF16, tune_emu, g_trace != nullptr)
                    : use_v4 ? pick_variant4(plan.kd, p->dtype == FA_SM100_BF16, tune_emu, tune_split, g_trace != nullptr)
                             : pick_variant2(plan.kd, p->dtype == FA_SM100_BF16, tune_halves, tune_emu,
                                             tune_split, g_trace != nullptr);
@@ -394,7 +421,7 @@ extern "C" int fa_sm100_fwd(const fa_sm100_fwd_params* p, void* stream) {
         cuuint64_t s_b = stride_bytes(es[0], p->batch, s_h * cuuint64_t(p->heads_kv));
         cuuint64_t dims[4] = {D, cuuint64_t(p->seqlen_kv), cuuint64_t(p->heads_kv), cuuint64_t(p->batch)};
         cuuint64_t strides[3] = {s_s, s_h, s_b};
-        cuuint32_t box[4] = {64, 128, 1, 1};
+        cuuint32_t box[4] = {64, cuuint32_t(use_v5 ? 64 : 128), 1, 1};
         return encode_map(m, dt, 4, base, dims, strides, box, what);
     };
     rc = encode_kv(&kp.tm_k, p->k, p->k_strides, "k");

@@ -91,6 +91,20 @@ __device__ __forceinline__ bool mbar_test_wait(uint32_t bar, uint32_t parity) {
     return ok != 0;
 }
 
+// try_wait with a suspend-time hint (ns): the thread sleeps in hardware until the phase completes
+// or roughly the hint elapses — an idle poller then costs its SM sub-partition no issue slots.
+__device__ __forceinline__ bool mbar_try_wait_hint(uint32_t bar, uint32_t parity, uint32_t hint_ns) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity), "r"(hint_ns)
+        : "memory");
+    return ok != 0;
+}
+
 // Bounded wait.  A protocol bug in a warp-specialised kernel otherwise hangs the GPU; here every
 // wait gives up after kWatchdogNs, records (code, bar, parity) in the status words and raises the
 // abort flag, after which all waits in the grid fall through so the kernel terminates normally

@@ -43,7 +43,7 @@ def main():
     k = torch.randn(B, Hkv, Sk, D, generator=g, device=dev).to(dt)
     v = torch.randn(B, Hkv, Sk, D, generator=g, device=dev).to(dt)
     flags = _lib.tune_flags(0 if args.emu is None else args.emu, 128 if args.split is None else args.split,
-                            2 if args.halves is None else args.halves)
+                            None if not args.halves else args.halves)
     for _ in range(2):
         ext.flash_attention_fwd(q, k, v, D ** -0.5, causal, flags)
     torch.cuda.synchronize()

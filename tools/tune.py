@@ -68,7 +68,7 @@ def main():
                   for e in [int(x) for x in args.emu.split(",")]]
         for halves, split, emu in combos:
             if True:
-                flags = _lib.tune_flags(emu, split, halves)
+                flags = _lib.tune_flags(emu, split, halves if halves else None)  # halves 0 = default generation (5)
                 try:
                     o = ext.flash_attention_fwd(q, k, v, scale, causal, flags)
                     _lib.check_device(0)
@@ -76,10 +76,10 @@ def main():
                     nan = int(torch.isnan(o.float()).sum())
                     ms = timeit(lambda: ext.flash_attention_fwd(q, k, v, scale, causal, flags), args.iters)
                     _lib.check_device(0)
-                    rec = dict(shape=name, kernel="v4" if halves == 3 else "v2", halves=halves, emu=emu, split=split, ms=ms, tflops=fl / ms / 1e9,
+                    rec = dict(shape=name, kernel={0: "v5", 3: "v4"}.get(halves, "v2"), halves=halves, emu=emu, split=split, ms=ms, tflops=fl / ms / 1e9,
                                max_abs_vs_v1=err, nan=nan)
                 except Exception as e:  # keep sweeping unless the device is gone
-                    rec = dict(shape=name, kernel="v4" if halves == 3 else "v2", halves=halves, emu=emu, split=split, error=repr(e)[:300])
+                    rec = dict(shape=name, kernel={0: "v5", 3: "v4"}.get(halves, "v2"), halves=halves, emu=emu, split=split, error=repr(e)[:300])
                     print(json.dumps(rec), flush=True)
                     out.append(rec)
                     if "ABORT" in repr(e) or "CUDA" in repr(e):
