@@ -18,6 +18,7 @@
 #include "fa_sm100_fwd.cuh"
 #include "fa_sm100_fwd4.cuh"
 #include "fa_sm100_fwd5.cuh"
+#include "fa_sm100_fwd6.cuh"
 
 namespace {
 
@@ -207,6 +208,34 @@ Variant2* pick_variant5(int kd, bool bf16, int emu, bool trace) {
     return bf16 ? variant5<64, true, E, false>() : variant5<64, false, E, false>();
 }
 
+// ---- generation-6 kernel variants (fa_sm100_fwd6.cuh): 128-key blocks, P handed over in parts ----
+template <int kD, bool kBf16, int kEmu, int kParts, bool kTrace>
+Variant2* variant6() {
+    constexpr int kStages = kD == 64 ? 8 : 5;
+    static Variant2 v{fa100::v6::fa_fwd_sm100_v6<kD, kBf16, kStages, kEmu, kParts, kTrace>,
+                      fa100::v6::Smem<kD, kStages>::kDynamicBytes, fa100::v6::Cfg::kNumThreads};
+    return &v;
+}
+constexpr int kDefEmu6 = 2, kDefParts6 = 2;
+// split flag 64 -> 4 parts, 96 -> 2 parts, 128 -> 1 part
+Variant2* pick_variant6(int kd, bool bf16, int emu, int split, bool trace) {
+    if (emu < 0) emu = kDefEmu6;
+    const int parts = split < 0 ? kDefParts6 : (split == 64 ? 4 : split == 96 ? 2 : 1);
+#ifdef FA_SM100_TUNE
+#define FA_V6(D, BF, E, PT)                                                                \
+    if (kd == D && bf16 == BF && emu == E && parts == PT)                                  \
+        return trace ? variant6<D, BF, E, PT, true>() : variant6<D, BF, E, PT, false>();
+    FA_V6(128, true, 0, 1) FA_V6(128, true, 0, 2) FA_V6(128, true, 0, 4)
+    FA_V6(128, true, 2, 1) FA_V6(128, true, 2, 2) FA_V6(128, true, 2, 4)
+    FA_V6(128, true, 3, 2) FA_V6(128, true, 3, 4) FA_V6(128, true, 1, 2) FA_V6(128, true, 1, 4)
+#undef FA_V6
+#endif
+    (void)trace;
+    constexpr int E = kDefEmu6, PT = kDefParts6;
+    if (kd == 128) return bf16 ? variant6<128, true, E, PT, false>() : variant6<128, false, E, PT, false>();
+    return bf16 ? variant6<64, true, E, PT, false>() : variant6<64, false, E, PT, false>();
+}
+
 Variant2* pick_variant2(int kd, bool bf16, int halves, int emu, int split, bool trace) {
     if (halves < 0) halves = kDefHalves;
     if (emu < 0) emu = kDefEmu;
@@ -227,7 +256,7 @@ constexpr int kDefaultGenStatic = 5;  // true: generation 4 (fa_sm100_fwd4.cuh) 
 // FA_SM100_GEN=2|4 in the environment overrides the default generation (test / tuning aid).
 const int kDefaultGen = [] {
     const char* e = getenv("FA_SM100_GEN");
-    if (e && (e[0] == '2' || e[0] == '4' || e[0] == '5')) return e[0] - '0';
+    if (e && (e[0] == '2' || e[0] == '4' || e[0] == '5' || e[0] == '6')) return e[0] - '0';
     return kDefaultGenStatic;
 }();
 long long* g_trace = nullptr;  // debug timeline buffer (fa_sm100_internal_set_trace)
@@ -325,8 +354,9 @@ extern "C" const char* fa_sm100_last_error(void) { return g_err; }
 extern "C" uint64_t fa_sm100_launch_count(void) { return g_launches.load(); }
 
 extern "C" const char* fa_sm100_build_info(void) {
-    return "fa_sm100: sm_100a tcgen05/TMEM/TMA FlashAttention-2 forward; variants D{64,128} x "
-           "{fp16,bf16}; 320 threads/CTA, 2x128-row M tiles, 128-col KV blocks";
+    return "fa_sm100: sm_100a tcgen05/TMEM/TMA FlashAttention-2 forward; default kernel "
+           "fa100::v5::fa_fwd_sm100_v5 (persistent, 512 threads/CTA, 2x128-row M tiles, 64-key half "
+           "blocks, 2 S buffers per tile); variants D{64,128} x {fp16,bf16}";
 }
 
 extern "C" int fa_sm100_plan(const fa_sm100_fwd_params* params, int32_t* grid, int32_t* smem_bytes,
@@ -369,8 +399,10 @@ extern "C" int fa_sm100_fwd(const fa_sm100_fwd_params* p, void* stream) {
     Variant* var = plan.var;
     const int tune_halves = int((p->flags >> 14) & 0x3u) == 0 ? -1 : int((p->flags >> 14) & 0x3u);
     const bool use_v4 = !use_v1 && tune_halves == 3;
-    const bool use_v5 = !use_v1 && tune_halves < 0 && kDefaultGen == 5;
+    const bool use_v5 = !use_v1 && ((tune_halves < 0 && kDefaultGen == 5) || tune_halves == 2);
+    const bool use_v6 = !use_v1 && tune_halves < 0 && kDefaultGen == 6;
     Variant2* var2 = use_v1 ? nullptr
+                   : use_v6 ? pick_variant6(plan.kd, p->dtype == FA_SM100_BF16, tune_emu, tune_split, g_trace != nullptr)
                    : use_v5 ? pick_variant5(plan.kd, p->dtype == FA_SM100_BF16, tune_emu, g_trace != nullptr)
                    : use_v4 ? pick_variant4(plan.kd, p->dtype == FA_SM100_BF16, tune_emu, tune_split, g_trace != nullptr)
                             : pick_variant2(plan.kd, p->dtype == FA_SM100_BF16, tune_halves, tune_emu,

@@ -64,7 +64,7 @@ def main():
             print(json.dumps(rec), flush=True)
             out.append(rec)
         combos = [(h, sp, e) for h in [int(x) for x in args.halves.split(",")]
-                  for sp in ([int(x) for x in args.split.split(",")] if h in (1, 3) else [128])
+                  for sp in ([int(x) for x in args.split.split(",")] if h in (0, 1, 3) else [128])
                   for e in [int(x) for x in args.emu.split(",")]]
         for halves, split, emu in combos:
             if True:
@@ -76,10 +76,10 @@ def main():
                     nan = int(torch.isnan(o.float()).sum())
                     ms = timeit(lambda: ext.flash_attention_fwd(q, k, v, scale, causal, flags), args.iters)
                     _lib.check_device(0)
-                    rec = dict(shape=name, kernel={0: "v5", 3: "v4"}.get(halves, "v2"), halves=halves, emu=emu, split=split, ms=ms, tflops=fl / ms / 1e9,
+                    rec = dict(shape=name, kernel={0: "v6", 2: "v5", 3: "v4"}.get(halves, "v2"), halves=halves, emu=emu, split=split, ms=ms, tflops=fl / ms / 1e9,
                                max_abs_vs_v1=err, nan=nan)
                 except Exception as e:  # keep sweeping unless the device is gone
-                    rec = dict(shape=name, kernel={0: "v5", 3: "v4"}.get(halves, "v2"), halves=halves, emu=emu, split=split, error=repr(e)[:300])
+                    rec = dict(shape=name, kernel={0: "v6", 2: "v5", 3: "v4"}.get(halves, "v2"), halves=halves, emu=emu, split=split, error=repr(e)[:300])
                     print(json.dumps(rec), flush=True)
                     out.append(rec)
                     if "ABORT" in repr(e) or "CUDA" in repr(e):
