@@ -68,7 +68,8 @@ struct Smem {
     static constexpr int kKV = 2 * kTileBytes;
     static constexpr int kHalfBytes = kTileBytes / 2;           // 64 keys of K or V
     static constexpr int kHalfPanel = kPanelBytes / 2;          // 64 rows x 64 16-bit elements
-    static constexpr int kRowSum = kKV + kStages * kHalfBytes;  // float [2][128] final row sums
+    static constexpr int kStageBytes = 2 * kHalfBytes;          // ring stage = two half tiles
+    static constexpr int kRowSum = kKV + kStages * kStageBytes;  // float [2][128] final row sums
     static constexpr int kTileRing = kRowSum + 2 * 128 * 4;      // int [kSchedDepth]
     static constexpr int kBars = kTileRing + 16;
     // barrier slots (8 B each)
@@ -78,7 +79,7 @@ struct Smem {
     static constexpr int kBarKVEmpty = 4 + kStages;      // [kStages]
     static constexpr int kBarSFull = 4 + 2 * kStages;    // [2][2]  MMA commit -> softmax   (tile, buffer)
     static constexpr int kBarPFull = 8 + 2 * kStages;    // [2][2]  softmax (4 warps) -> MMA (tile, buffer)
-    static constexpr int kBarPVDone = 12 + 2 * kStages;  // [2]     MMA commit after every P·V (rescale guard)
+    static constexpr int kBarPVDone = 12 + 2 * kStages;  // [2]     MMA commit after the last two P·V of a tile (rescale guard)
     static constexpr int kBarRowSum = 14 + 2 * kStages;  // [2]     softmax (4 warps) -> epilogue
     static constexpr int kBarOFull = 16 + 2 * kStages;   // [2]     MMA commit -> epilogue
     static constexpr int kBarOEmpty = 18 + 2 * kStages;  // [2]     epilogue (4 warps) -> MMA
@@ -196,22 +197,24 @@ fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
                     }
                 }
                 tr.ev(1);
-                // 64-key half tiles in the order the MMA issuer consumes them:
-                //   K0 K1 | V0 K2 | V1 K3 | ... | V(nh-3) K(nh-1) | V(nh-2) | V(nh-1)
-                const int nh = 4 * w.nmax / 2;  // half-blocks of the longer M-tile
-                for (int it = 0; it < 2 * nh; ++it) {
-                    bool is_v;
-                    int h;
-                    if (it < 2) { is_v = false; h = it; }
-                    else if (it == 2 * nh - 1) { is_v = true; h = nh - 1; }
-                    else { const int rr = it - 2; is_v = (rr & 1) == 0; h = is_v ? (rr >> 1) : (rr >> 1) + 2; }
-                    const CUtensorMap* tm = is_v ? &params.tm_v : &params.tm_k;
+                // Ring stages of two 64-key half tiles, in the order the MMA issuers consume them
+                // (one full/empty barrier pair per stage, so an issuer does one wait and one
+                // commit per half-block):
+                //   {K0,K1} {V0,K2} {V1,K3} ... {V(nh-3),K(nh-1)} {V(nh-2),V(nh-1)}
+                const int nh = 2 * w.nmax;  // half-blocks of the longer M-tile
+                for (int i = 0; i < nh; ++i) {
+                    const CUtensorMap* tm0 = (i == 0) ? &params.tm_k : &params.tm_v;
+                    const CUtensorMap* tm1 = (i == nh - 1) ? &params.tm_v : &params.tm_k;
+                    const int h0 = (i == 0) ? 0 : i - 1;
+                    const int h1 = (i == nh - 1) ? nh - 1 : i + 1;
                     mbar_wait(bar(L::kBarKVEmpty + slot), phase ^ 1u, status, 1);
                     const uint32_t fb = bar(L::kBarKVFull + slot);
-                    mbar_arrive_expect_tx(fb, kHalfBytes);
+                    mbar_arrive_expect_tx(fb, 2 * kHalfBytes);
+                    const uint32_t dst = smem_base + L::kKV + slot * (2 * kHalfBytes);
                     for (int pn = 0; pn < kPanels; ++pn)
-                        tma_load_4d(smem_base + L::kKV + slot * kHalfBytes + pn * kHalfPanel, tm, fb,
-                                    pn * 64, h * 64, w.kv_head, w.b);
+                        tma_load_4d(dst + pn * kHalfPanel, tm0, fb, pn * 64, h0 * 64, w.kv_head, w.b);
+                    for (int pn = 0; pn < kPanels; ++pn)
+                        tma_load_4d(dst + kHalfBytes + pn * kHalfPanel, tm1, fb, pn * 64, h1 * 64, w.kv_head, w.b);
                     if (++slot == kStages) { slot = 0; phase ^= 1u; }
                 }
             }
@@ -273,28 +276,26 @@ fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
                 };
                 const int nh = 2 * w.nblk[t];
                 const int nhmax = 2 * w.nmax;
-                auto idx_k = [](int h) { return h < 2 ? h : 2 * h - 1; };
-                auto idx_v = [&](int h) { return h == nhmax - 1 ? 2 * nhmax - 1 : 2 + 2 * h; };
-                // wait for a half tile; returns its slot
-                auto acquire = [&](int it, uint32_t code) {
+                // wait for ring stage i of this work tile; returns the index of its first half slot
+                auto acquire = [&](int i, uint32_t code) {
                     int sl; uint32_t ph;
-                    ring(it, sl, ph);
+                    ring(i, sl, ph);
                     mbar_wait(bar(L::kBarKVFull + sl), ph, status, code);
                     return sl;
                 };
                 if (nh > 0) {
-                    // prologue: S(0), S(1)
+                    // prologue: S(0), S(1) from stage 0 = {K0, K1}
                     mbar_wait(bar(L::kBarQFull + t), q_phase, status, 3);
                     q_phase ^= 1u;
-#pragma unroll
-                    for (int hh = 0; hh < 2; ++hh) {
-                        const int ks = acquire(idx_k(hh), 2);
-                        issue_s(t, hh, ks);
-                        tc_commit(bar(L::kBarSFull + 2 * t + hh));
-                        tc_commit(bar(L::kBarKVEmpty + ks));
-                    }
+                    const int s0 = acquire(0, 2);
+                    issue_s(t, 0, 2 * s0);
+                    tc_commit(bar(L::kBarSFull + 2 * t + 0));
+                    issue_s(t, 1, 2 * s0 + 1);
+                    tc_commit(bar(L::kBarSFull + 2 * t + 1));
+                    tc_commit(bar(L::kBarKVEmpty + s0));
                     if (nh == 2) tc_commit(bar(L::kBarQEmpty + t));
                     tr.ev(2);
+                    int st = 0;  // stage holding V(h): stage h+1 {V(h), K(h+2)}, or the last one {V(nh-2), V(nh-1)}
                     for (int h = 0; h < nh; ++h) {
                         const int b = h & 1;
                         mbar_wait(bar(L::kBarPFull + 2 * t + b), (blk_base + (h >> 1)) & 1u, status, 5);
@@ -302,33 +303,30 @@ fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
                             mbar_wait(bar(L::kBarOEmpty + t), oe_phase ^ 1u, status, 11);
                             oe_phase ^= 1u;
                         }
-                        const int vs = acquire(idx_v(h), 4);
-                        if (kFenceMma) tc_fence_after_sync();
+                        const bool tail = (h == nhmax - 1);  // V(nhmax-1) sits in the second half of the last stage
+                        if (!tail) st = acquire(h + 1, 4);
                         tr.ev(3);
-                        issue_pv(t, b, vs, h > 0);
-                        tc_commit(bar(L::kBarPVDone + t));
-                        tc_commit(bar(L::kBarKVEmpty + vs));
+                        issue_pv(t, b, 2 * st + (tail ? 1 : 0), h > 0);
                         if (h + 2 < nh) {
-                            const int ks = acquire(idx_k(h + 2), 6);
-                            issue_s(t, b, ks);
+                            issue_s(t, b, 2 * st + 1);
                             tc_commit(bar(L::kBarSFull + 2 * t + b));
-                            tc_commit(bar(L::kBarKVEmpty + ks));
                             if (h + 3 == nh) tc_commit(bar(L::kBarQEmpty + t));
+                        } else {
+                            tc_commit(bar(L::kBarPVDone + t));  // no S follows: the rescale guard of the last steps
                         }
+                        if (h + 1 < nhmax - 1 || tail) tc_commit(bar(L::kBarKVEmpty + st));
                         if (h + 1 == nh) tc_commit(bar(L::kBarOFull + t));
                         tr.ev(5);
                     }
                 }
-                // half tiles only the other (longer) M-tile uses: stay in lockstep with the ring
-                for (int h = nh; h < nhmax; ++h) {
-                    const int ks = acquire(idx_k(h), 16);
-                    mbar_arrive(bar(L::kBarKVEmpty + ks));
-                    const int vs = acquire(idx_v(h), 17);
-                    mbar_arrive(bar(L::kBarKVEmpty + vs));
+                // stages only the other (longer) M-tile uses: stay in lockstep with the ring
+                for (int i = (nh > 0 ? nh + 1 : 0); i < nhmax; ++i) {
+                    const int sl = acquire(i, 16);
+                    mbar_arrive(bar(L::kBarKVEmpty + sl));
                 }
                 blk_base += static_cast<uint32_t>(w.nblk[t]);
                 {
-                    const int x = slot0 + 4 * w.nmax;  // 2 nhmax half tiles
+                    const int x = slot0 + 2 * w.nmax;  // nhmax stages
                     const int q = x / kStages;
                     slot0 = x - q * kStages;
                     phase0 ^= static_cast<uint32_t>(q & 1);
@@ -488,9 +486,12 @@ fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
                     }
                     if (h > 0) {
                         // O_t must be quiescent: P·V(h-1) complete (P·V(h) cannot have been issued,
-                        // P(h) is not published yet).  One PVDone phase per half-block.
+                        // P(h) is not published yet).
                         tr.ev(7);
-                        mbar_wait(bar(L::kBarPVDone + t), (h - 1) & 1u, status, 15);
+                        if (h + 1 < 2 * n)  // S(h+1) was committed behind P·V(h-1): wait without consuming
+                            mbar_wait(bar(L::kBarSFull + 2 * t + (b ^ 1)), (blk_base + ((h + 1) >> 1)) & 1u, status, 15);
+                        else                // last half-block: P·V(2n-2) is the first of this tile's two PVDone commits
+                            mbar_wait(bar(L::kBarPVDone + t), 0u, status, 15);
                         tc_fence_after_sync();
 #pragma unroll
                         for (int c = 0; c < kD / 32; ++c) {

@@ -186,7 +186,7 @@ Variant2* pick_variant4(int kd, bool bf16, int emu, int split, bool trace) {
 // ---- generation-5 kernel variants (fa_sm100_fwd5.cuh): half-block pipeline ----
 template <int kD, bool kBf16, int kEmu, bool kTrace>
 Variant2* variant5() {
-    constexpr int kStages = kD == 64 ? 16 : 10;  // 64-key half tiles of K / V
+    constexpr int kStages = kD == 64 ? 8 : 5;  // ring stages of two 64-key half tiles of K / V
     static Variant2 v{fa100::v5::fa_fwd_sm100_v5<kD, kBf16, kStages, kEmu, kTrace>,
                       fa100::v5::Smem<kD, kStages>::kDynamicBytes, fa100::v5::Cfg::kNumThreads};
     return &v;

@@ -76,10 +76,10 @@ def main():
                     nan = int(torch.isnan(o.float()).sum())
                     ms = timeit(lambda: ext.flash_attention_fwd(q, k, v, scale, causal, flags), args.iters)
                     _lib.check_device(0)
-                    rec = dict(shape=name, kernel={0: "v6", 2: "v5", 3: "v4"}.get(halves, "v2"), halves=halves, emu=emu, split=split, ms=ms, tflops=fl / ms / 1e9,
+                    rec = dict(shape=name, kernel={0: "default(v5)", 2: "v5", 3: "v4"}.get(halves, "v2"), halves=halves, emu=emu, split=split, ms=ms, tflops=fl / ms / 1e9,
                                max_abs_vs_v1=err, nan=nan)
                 except Exception as e:  # keep sweeping unless the device is gone
-                    rec = dict(shape=name, kernel={0: "v6", 2: "v5", 3: "v4"}.get(halves, "v2"), halves=halves, emu=emu, split=split, error=repr(e)[:300])
+                    rec = dict(shape=name, kernel={0: "default(v5)", 2: "v5", 3: "v4"}.get(halves, "v2"), halves=halves, emu=emu, split=split, error=repr(e)[:300])
                     print(json.dumps(rec), flush=True)
                     out.append(rec)
                     if "ABORT" in repr(e) or "CUDA" in repr(e):
