@@ -93,7 +93,8 @@ struct Smem {
 
 
 // kEmu: of every 8 element pairs, how many take the FMA-pipe exp2 (0 = all MUFU).
-template <int kD, bool kBf16, int kStages, int kEmu, bool kTrace>
+// kSpec: speculative stale-max fast path in the softmax (row max reduced under the first exp2 chunk).
+template <int kD, bool kBf16, int kStages, int kEmu, bool kSpec, bool kTrace>
 __global__ void __launch_bounds__(Cfg::kNumThreads, 1)
 fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
     using L = Smem<kD, kStages>;
@@ -447,71 +448,8 @@ fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
                 tmem_wait_ld();
                 tr.ev(2);
 
-                // element mask only on half-blocks that cross the diagonal or the end of K
-                const int col0 = h * 64;
-                const bool need_mask = (col0 + 64 > params.seqlen_k) ||
-                                       (params.causal && (col0 + 63 > my_pos0 + causal_off));
-                if (need_mask) {
-                    const int rel = row_limit - col0;
-#pragma unroll
-                    for (int i = 0; i < 64; ++i)
-                        if (i > rel) s[i] = 0xff800000u;  // -inf
-                }
-
-                float mx0 = max3(__uint_as_float(s[0]), __uint_as_float(s[1]), __uint_as_float(s[2]));
-                float mx1 = max3(__uint_as_float(s[3]), __uint_as_float(s[4]), __uint_as_float(s[5]));
-                float mx2 = max3(__uint_as_float(s[6]), __uint_as_float(s[7]), __uint_as_float(s[8]));
-                float mx3 = max3(__uint_as_float(s[9]), __uint_as_float(s[10]), __uint_as_float(s[11]));
-#pragma unroll
-                for (int i = 12; i < 60; i += 8) {
-                    mx0 = max3(mx0, __uint_as_float(s[i]), __uint_as_float(s[i + 1]));
-                    mx1 = max3(mx1, __uint_as_float(s[i + 2]), __uint_as_float(s[i + 3]));
-                    mx2 = max3(mx2, __uint_as_float(s[i + 4]), __uint_as_float(s[i + 5]));
-                    mx3 = max3(mx3, __uint_as_float(s[i + 6]), __uint_as_float(s[i + 7]));
-                }
-                mx0 = max3(mx0, __uint_as_float(s[60]), __uint_as_float(s[61]));
-                mx1 = max3(mx1, __uint_as_float(s[62]), __uint_as_float(s[63]));
-                const float m_new = fmaxf(max3(m, mx0, mx1), fmaxf(mx2, mx3));
-
-                // lazy rescale: keep the stale max unless this row grew by more than 2^8
-                const bool grow = (m_new - m) * scale_log2 > kRescaleThreshold;  // false for NaN (-inf - -inf)
-                if (__any_sync(0xffffffffu, grow)) {
-                    float alpha = 1.f;
-                    if (grow) {
-                        alpha = ex2_approx((m - m_new) * scale_log2);
-                        m = m_new;
-                        msc = m * scale_log2;
-                        nm2 = pack_f32x2(-msc, -msc);
-                        l *= alpha;
-                    }
-                    if (h > 0) {
-                        // O_t must be quiescent: P·V(h-1) complete (P·V(h) cannot have been issued,
-                        // P(h) is not published yet).
-                        tr.ev(7);
-                        if (h + 1 < 2 * n)  // S(h+1) was committed behind P·V(h-1): wait without consuming
-                            mbar_wait(bar(L::kBarSFull + 2 * t + (b ^ 1)), (blk_base + ((h + 1) >> 1)) & 1u, status, 15);
-                        else                // last half-block: P·V(2n-2) is the first of this tile's two PVDone commits
-                            mbar_wait(bar(L::kBarPVDone + t), 0u, status, 15);
-                        tc_fence_after_sync();
-#pragma unroll
-                        for (int c = 0; c < kD / 32; ++c) {
-                            uint32_t o[32];
-                            tmem_ld32(tmem_o + c * 32, o);
-                            tmem_wait_ld();
-#pragma unroll
-                            for (int i = 0; i < 32; ++i)
-                                o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-                            tmem_st32(tmem_o + c * 32, o);
-                        }
-                        tmem_wait_st();
-                    }
-                }
-                tr.ev(3);
-
-                // exp2 of 64 keys -> 32 packed columns of P, stored straight back over S
-                uint64_t la = pack_f32x2(0.f, 0.f), lb = pack_f32x2(0.f, 0.f);
-#pragma unroll
-                for (int c = 0; c < 2; ++c) {
+                // exp2 of 32 keys -> 16 packed columns of P, stored straight back over S
+                auto exp_chunk = [&](int c, uint64_t& sa, uint64_t& sb) {
                     uint32_t pk[16];
 #pragma unroll
                     for (int q = 0; q < 16; ++q) {
@@ -527,12 +465,90 @@ fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
                             p0 = ex2_approx(x0);
                             p1 = ex2_approx(x1);
                         }
-                        if (q & 1) lb = add_f32x2(lb, pack_f32x2(p0, p1));
-                        else la = add_f32x2(la, pack_f32x2(p0, p1));
+                        if (q & 1) sb = add_f32x2(sb, pack_f32x2(p0, p1));
+                        else sa = add_f32x2(sa, pack_f32x2(p0, p1));
                         pk[q] = pack2<kBf16>(p0, p1);
                     }
                     tmem_st16(tmem_s + b * 64 + c * 16, pk);
+                };
+                auto row_max = [&]() -> float {
+                    float mx0 = max3(__uint_as_float(s[0]), __uint_as_float(s[1]), __uint_as_float(s[2]));
+                    float mx1 = max3(__uint_as_float(s[3]), __uint_as_float(s[4]), __uint_as_float(s[5]));
+                    float mx2 = max3(__uint_as_float(s[6]), __uint_as_float(s[7]), __uint_as_float(s[8]));
+                    float mx3 = max3(__uint_as_float(s[9]), __uint_as_float(s[10]), __uint_as_float(s[11]));
+#pragma unroll
+                    for (int i = 12; i < 60; i += 8) {
+                        mx0 = max3(mx0, __uint_as_float(s[i]), __uint_as_float(s[i + 1]));
+                        mx1 = max3(mx1, __uint_as_float(s[i + 2]), __uint_as_float(s[i + 3]));
+                        mx2 = max3(mx2, __uint_as_float(s[i + 4]), __uint_as_float(s[i + 5]));
+                        mx3 = max3(mx3, __uint_as_float(s[i + 6]), __uint_as_float(s[i + 7]));
+                    }
+                    mx0 = max3(mx0, __uint_as_float(s[60]), __uint_as_float(s[61]));
+                    mx1 = max3(mx1, __uint_as_float(s[62]), __uint_as_float(s[63]));
+                    return fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+                };
+
+                // element mask only on half-blocks that cross the diagonal or the end of K
+                const int col0 = h * 64;
+                const bool need_mask = (col0 + 64 > params.seqlen_k) ||
+                                       (params.causal && (col0 + 63 > my_pos0 + causal_off));
+                uint64_t la = pack_f32x2(0.f, 0.f), lb = pack_f32x2(0.f, 0.f);
+
+                // Fast path (all but the first and the masked half-blocks): the first 32 keys are
+                // exponentiated against the stale running max while the row max of the half-block
+                // is reduced in the shadow of those MUFU ops; the result stands unless some row of
+                // this warp grew past the lazy-rescale threshold (then the half-block is redone —
+                // the scores are still in registers, P chunk 0 is overwritten, nothing is published).
+                bool fast = false;
+                if (kSpec && h > 0 && !need_mask) {
+                    uint64_t sa = pack_f32x2(0.f, 0.f), sb = pack_f32x2(0.f, 0.f);
+                    exp_chunk(0, sa, sb);
+                    const float mx = row_max();
+                    fast = !__any_sync(0xffffffffu, (mx - m) * scale_log2 > kRescaleThreshold);
+                    if (fast) { la = sa; lb = sb; }
                 }
+                if (!fast) {
+                    if (need_mask) {
+                        const int rel = row_limit - col0;
+#pragma unroll
+                        for (int i = 0; i < 64; ++i)
+                            if (i > rel) s[i] = 0xff800000u;  // -inf
+                    }
+                    const float m_new = fmaxf(m, row_max());
+                    // lazy rescale: keep the stale max unless this row grew by more than 2^8
+                    float alpha = 1.f;
+                    if ((m_new - m) * scale_log2 > kRescaleThreshold) {  // false for NaN (-inf - -inf)
+                        alpha = ex2_approx((m - m_new) * scale_log2);
+                        m = m_new;
+                        msc = m * scale_log2;
+                        nm2 = pack_f32x2(-msc, -msc);
+                        l *= alpha;
+                    }
+                    if (h > 0 && __any_sync(0xffffffffu, alpha != 1.f)) {
+                        // O_t must be quiescent: P·V(h-1) complete (P·V(h) cannot have been issued,
+                        // P(h) is not published yet).
+                        tr.ev(7);
+                        if (h + 1 < 2 * n)  // S(h+1) was committed behind P·V(h-1): wait without consuming
+                            mbar_wait(bar(L::kBarSFull + 2 * t + (b ^ 1)), (blk_base + ((h + 1) >> 1)) & 1u, status, 15);
+                        else                // last half-block: P·V(2n-2) is the first of this tile's two PVDone commits
+                            mbar_wait(bar(L::kBarPVDone + t), 0u, status, 15);
+                        tc_fence_after_sync();
+#pragma unroll 1
+                        for (int c = 0; c < kD / 8; ++c) {
+                            uint32_t o[8];
+                            tmem_ld8(tmem_o + c * 8, o);
+                            tmem_wait_ld();
+#pragma unroll
+                            for (int i = 0; i < 8; ++i)
+                                o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+                            tmem_st8(tmem_o + c * 8, o);
+                        }
+                        tmem_wait_st();
+                    }
+                    exp_chunk(0, la, lb);
+                }
+                tr.ev(3);
+                exp_chunk(1, la, lb);
                 tmem_wait_st();
                 tc_fence_before_sync();
                 __syncwarp();

@@ -184,28 +184,37 @@ Variant2* pick_variant4(int kd, bool bf16, int emu, int split, bool trace) {
 }
 
 // ---- generation-5 kernel variants (fa_sm100_fwd5.cuh): half-block pipeline ----
-template <int kD, bool kBf16, int kEmu, bool kTrace>
+template <int kD, bool kBf16, int kEmu, bool kSpec, bool kTrace>
 Variant2* variant5() {
     constexpr int kStages = kD == 64 ? 8 : 5;  // ring stages of two 64-key half tiles of K / V
-    static Variant2 v{fa100::v5::fa_fwd_sm100_v5<kD, kBf16, kStages, kEmu, kTrace>,
+    static Variant2 v{fa100::v5::fa_fwd_sm100_v5<kD, kBf16, kStages, kEmu, kSpec, kTrace>,
                       fa100::v5::Smem<kD, kStages>::kDynamicBytes, fa100::v5::Cfg::kNumThreads};
     return &v;
 }
-constexpr int kDefEmu5 = 2;
-Variant2* pick_variant5(int kd, bool bf16, int emu, bool trace) {
-    if (emu < 0) emu = kDefEmu5;
+// Defaults from the interleaved A/B sweep in profiles/r01/ab_v5_emu_spec.log: D=128 -> 3 of 8 pairs on
+// the FMA pipe, plain two-pass softmax; D=64 -> 2 of 8, speculative stale-max softmax.
+constexpr int kDefEmu5_128 = 3, kDefEmu5_64 = 2;
+constexpr bool kDefSpec5_128 = false, kDefSpec5_64 = true;
+// split flag 64 selects the speculative-max softmax, 128 the two-pass one (tuning builds)
+Variant2* pick_variant5(int kd, bool bf16, int emu, int split, bool trace) {
+    if (emu < 0) emu = kd == 128 ? kDefEmu5_128 : kDefEmu5_64;
+    const bool spec = split < 0 ? (kd == 128 ? kDefSpec5_128 : kDefSpec5_64) : split == 64;
 #ifdef FA_SM100_TUNE
-#define FA_V5(D, BF, E)                                                                    \
-    if (kd == D && bf16 == BF && emu == E)                                                 \
-        return trace ? variant5<D, BF, E, true>() : variant5<D, BF, E, false>();
-    FA_V5(128, true, 0) FA_V5(128, true, 1) FA_V5(128, true, 2) FA_V5(128, true, 3) FA_V5(128, true, 4)
-    FA_V5(64, false, 0) FA_V5(64, false, 1) FA_V5(64, false, 2) FA_V5(64, false, 3)
+#define FA_V5(D, BF, E, SP)                                                                \
+    if (kd == D && bf16 == BF && emu == E && spec == SP)                                   \
+        return trace ? variant5<D, BF, E, SP, true>() : variant5<D, BF, E, SP, false>();
+    FA_V5(128, true, 0, false) FA_V5(128, true, 1, false) FA_V5(128, true, 2, false) FA_V5(128, true, 3, false)
+    FA_V5(128, true, 1, true) FA_V5(128, true, 2, true) FA_V5(128, true, 3, true)
+    FA_V5(64, false, 1, false) FA_V5(64, false, 2, false) FA_V5(64, false, 3, false)
+    FA_V5(64, false, 2, true) FA_V5(64, false, 3, true)
 #undef FA_V5
 #endif
     (void)trace;
-    constexpr int E = kDefEmu5;
-    if (kd == 128) return bf16 ? variant5<128, true, E, false>() : variant5<128, false, E, false>();
-    return bf16 ? variant5<64, true, E, false>() : variant5<64, false, E, false>();
+    if (kd == 128)
+        return bf16 ? variant5<128, true, kDefEmu5_128, kDefSpec5_128, false>()
+                    : variant5<128, false, kDefEmu5_128, kDefSpec5_128, false>();
+    return bf16 ? variant5<64, true, kDefEmu5_64, kDefSpec5_64, false>()
+                : variant5<64, false, kDefEmu5_64, kDefSpec5_64, false>();
 }
 
 // ---- generation-6 kernel variants (fa_sm100_fwd6.cuh): 128-key blocks, P handed over in parts ----
@@ -403,7 +412,7 @@ extern "C" int fa_sm100_fwd(const fa_sm100_fwd_params* p, void* stream) {
     const bool use_v6 = !use_v1 && tune_halves < 0 && kDefaultGen == 6;
     Variant2* var2 = use_v1 ? nullptr
                    : use_v6 ? pick_variant6(plan.kd, p->dtype == FA_SM100_BF16, tune_emu, tune_split, g_trace != nullptr)
-                   : use_v5 ? pick_variant5(plan.kd, p->dtype == FA_SM100_BF16, tune_emu, g_trace != nullptr)
+                   : use_v5 ? pick_variant5(plan.kd, p->dtype == FA_SM100_BF16, tune_emu, tune_split, g_trace != nullptr)
                    : use_v4 ? pick_variant4(plan.kd, p->dtype == FA_SM100_BF16, tune_emu, tune_split, g_trace != nullptr)
                             : pick_variant2(plan.kd, p->dtype == FA_SM100_BF16, tune_halves, tune_emu,
                                             tune_split, g_trace != nullptr);
