@@ -185,18 +185,22 @@ fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
                 // prefetch the next index; the atomic's latency hides behind this tile's TMA issue
                 next_idx = int(gridDim.x) + atomicAdd(params.sched, 1);
                 decode_tile(params, idx, w);
-#pragma unroll
-                for (int t = 0; t < 2; ++t) {
-                    if (w.nblk[t] > 0) {
-                        mbar_wait(bar(L::kBarQEmpty + t), qe_phase[t] ^ 1u, status, 10);
-                        qe_phase[t] ^= 1u;
-                        const uint32_t qbar = bar(L::kBarQFull + t);
-                        mbar_arrive_expect_tx(qbar, params.q_tile_bytes);
-                        for (int pn = 0; pn < kPanels; ++pn)
-                            tma_load_5d(smem_base + (t ? L::kQ1 : L::kQ0) + pn * kPanelBytes,
-                                        &params.tm_q, qbar, pn * 64, w.pos0[t], w.g_coord, w.kv_head, w.b);
-                    }
-                }
+                // Q_t of the new work tile goes out as soon as M-tile t of the previous one has issued
+                // its last S (QEmpty) — independently for the two tiles, and interleaved with the K/V
+                // stages below, so the tile that finishes first restarts without waiting for the other.
+                bool q_pending[2] = {w.nblk[0] > 0, w.nblk[1] > 0};
+                auto try_q = [&](int t, bool block) {
+                    if (!q_pending[t]) return;
+                    if (block) mbar_wait(bar(L::kBarQEmpty + t), qe_phase[t] ^ 1u, status, 10);
+                    else if (!mbar_test_wait(bar(L::kBarQEmpty + t), qe_phase[t] ^ 1u)) return;
+                    qe_phase[t] ^= 1u;
+                    const uint32_t qbar = bar(L::kBarQFull + t);
+                    mbar_arrive_expect_tx(qbar, params.q_tile_bytes);
+                    for (int pn = 0; pn < kPanels; ++pn)
+                        tma_load_5d(smem_base + (t ? L::kQ1 : L::kQ0) + pn * kPanelBytes,
+                                    &params.tm_q, qbar, pn * 64, w.pos0[t], w.g_coord, w.kv_head, w.b);
+                    q_pending[t] = false;
+                };
                 tr.ev(1);
                 // Ring stages of two 64-key half tiles, in the order the MMA issuers consume them
                 // (one full/empty barrier pair per stage, so an issuer does one wait and one
@@ -208,6 +212,15 @@ fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
                     const CUtensorMap* tm1 = (i == nh - 1) ? &params.tm_v : &params.tm_k;
                     const int h0 = (i == 0) ? 0 : i - 1;
                     const int h1 = (i == nh - 1) ? nh - 1 : i + 1;
+                    // While a Q tile is still pending the wait for a ring slot must not block: the slot
+                    // may only be released by MMAs that need that Q.
+                    while (q_pending[0] || q_pending[1]) {
+                        try_q(0, false);
+                        try_q(1, false);
+                        if (mbar_test_wait(bar(L::kBarKVEmpty + slot), phase ^ 1u)) break;
+                        __nanosleep(64);
+                        if (*reinterpret_cast<volatile unsigned int*>(status) != 0u) break;  // watchdog elsewhere
+                    }
                     mbar_wait(bar(L::kBarKVEmpty + slot), phase ^ 1u, status, 1);
                     const uint32_t fb = bar(L::kBarKVFull + slot);
                     mbar_arrive_expect_tx(fb, 2 * kHalfBytes);
@@ -218,6 +231,8 @@ fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
                         tma_load_4d(dst + kHalfBytes + pn * kHalfPanel, tm1, fb, pn * 64, h1 * 64, w.kv_head, w.b);
                     if (++slot == kStages) { slot = 0; phase ^= 1u; }
                 }
+                try_q(0, true);
+                try_q(1, true);
             }
         } else if ((warp == kMmaWarp || warp == kMmaWarp + 1) && elected) {
             // =========================== MMA issuer ===========================
