@@ -37,7 +37,6 @@ namespace v5 {
 
 using v4::Tile;
 using v4::decode_tile;
-using v4::TileConsumer;
 using v4::Tracer;
 using v4::kSchedDepth;
 using v4::kPanelBytes;
@@ -49,6 +48,7 @@ struct Cfg {
     static constexpr int kEpiWarp0 = 8;
     static constexpr int kMmaWarp = 12;   // 12: M-tile 0, 13: M-tile 1
     static constexpr int kLoadWarp = 14;
+    static constexpr int kQWarp = 15;
     static constexpr int kNumWarps = 16;
     static constexpr int kNumThreads = kNumWarps * 32;
     static constexpr int kRegsLaunch = 128;  // 64K / 512
@@ -70,8 +70,9 @@ struct Smem {
     static constexpr int kHalfPanel = kPanelBytes / 2;          // 64 rows x 64 16-bit elements
     static constexpr int kStageBytes = 2 * kHalfBytes;          // ring stage = two half tiles
     static constexpr int kRowSum = kKV + kStages * kStageBytes;  // float [2][128] final row sums
-    static constexpr int kTileRing = kRowSum + 2 * 128 * 4;      // int [kSchedDepth]
-    static constexpr int kBars = kTileRing + 16;
+    static constexpr int kTileRec = 48;                           // decoded work tile: 12 ints
+    static constexpr int kTileRing = kRowSum + 2 * 128 * 4;      // [kSchedDepth] records
+    static constexpr int kBars = kTileRing + kSchedDepth * kTileRec;
     // barrier slots (8 B each)
     static constexpr int kBarQFull = 0;                  // [2]     TMA -> MMA
     static constexpr int kBarQEmpty = 2;                 // [2]     MMA commit -> TMA
@@ -91,6 +92,38 @@ struct Smem {
     static constexpr int kDynamicBytes = kTotal;
 };
 
+// Work-tile hand-off.  The producer thread decodes each tile index once (decode_tile is a chain of
+// integer divisions: some 3000 cycles for a lone thread on a busy scheduler, measured) and publishes
+// the decoded record through the shared-memory ring, one tile ahead of the consumers; they only
+// copy it out.  mblock < 0 ends the CTA.
+template <typename L>
+__device__ __forceinline__ void tile_store(uint32_t smem_base, int slot, const Tile& t) {
+    const uint32_t a = smem_base + L::kTileRing + slot * L::kTileRec;
+    asm volatile("st.shared.v4.s32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(t.mblock), "r"(t.hu), "r"(t.b), "r"(t.kv_head) : "memory");
+    asm volatile("st.shared.v4.s32 [%0], {%1, %2, %3, %4};" ::"r"(a + 16), "r"(t.g_coord), "r"(t.pos0[0]), "r"(t.pos0[1]), "r"(t.nblk[0]) : "memory");
+    asm volatile("st.shared.v2.s32 [%0], {%1, %2};" ::"r"(a + 32), "r"(t.nblk[1]), "r"(t.nmax) : "memory");
+}
+template <typename L>
+struct TileConsumer {
+    uint32_t smem_base;
+    int round = 0;
+    unsigned int* status;
+    __device__ __forceinline__ TileConsumer(uint32_t base, unsigned int* st) : smem_base(base), status(st) {}
+    // all lanes of a consumer warp call this together (or the single active thread of a role)
+    __device__ __forceinline__ bool next(Tile& t, bool elected) {
+        const int slot = round % kSchedDepth;
+        const uint32_t parity = (round / kSchedDepth) & 1;
+        mbar_wait(smem_base + L::kBars + (L::kBarTileFull + slot) * 8, parity, status, 20);
+        const uint32_t a = smem_base + L::kTileRing + slot * L::kTileRec;
+        asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(t.mblock), "=r"(t.hu), "=r"(t.b), "=r"(t.kv_head) : "r"(a) : "memory");
+        asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(t.g_coord), "=r"(t.pos0[0]), "=r"(t.pos0[1]), "=r"(t.nblk[0]) : "r"(a + 16) : "memory");
+        asm volatile("ld.shared.v2.s32 {%0, %1}, [%2];" : "=r"(t.nblk[1]), "=r"(t.nmax) : "r"(a + 32) : "memory");
+        __syncwarp(__activemask());
+        if (elected) mbar_arrive(smem_base + L::kBars + (L::kBarTileEmpty + slot) * 8);
+        ++round;
+        return t.mblock >= 0;
+    }
+};
 
 // kEmu: of every 8 element pairs, how many take the FMA-pipe exp2 (0 = all MUFU).
 // kSpec: speculative stale-max fast path in the softmax (row max reduced under the first exp2 chunk).
@@ -99,7 +132,7 @@ __global__ void __launch_bounds__(Cfg::kNumThreads, 1)
 fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
     using L = Smem<kD, kStages>;
     using C = Cfg;
-    constexpr int kEpiWarp0 = C::kEpiWarp0, kMmaWarp = C::kMmaWarp, kLoadWarp = C::kLoadWarp;
+    constexpr int kEpiWarp0 = C::kEpiWarp0, kMmaWarp = C::kMmaWarp, kLoadWarp = C::kLoadWarp, kQWarp = C::kQWarp;
     constexpr int kPanels = L::kPanels;
     constexpr uint32_t kHalfBytes = L::kHalfBytes;
     constexpr uint32_t kHalfPanel = L::kHalfPanel;
@@ -145,7 +178,7 @@ fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
         }
         for (int s = 0; s < kSchedDepth; ++s) {
             mbar_init(bar(L::kBarTileFull + s), 1);
-            mbar_init(bar(L::kBarTileEmpty + s), C::kSoftmaxWarps + 4 + 2);  // softmax + epilogue + 2 MMA
+            mbar_init(bar(L::kBarTileEmpty + s), C::kSoftmaxWarps + 4 + 3);  // softmax + epilogue + 2 MMA + Q loader
         }
         fence_mbar_init();
     }
@@ -171,35 +204,29 @@ fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
             tr.init(params, 4, true);
             int slot = 0;
             uint32_t phase = 0;
-            uint32_t qe_phase[2] = {0, 0};
-            Tile w;
-            int next_idx = blockIdx.x;  // first tile: no atomic
-            for (int round = 0;; ++round) {
-                // publish this round's tile index (or the end marker) to the other warps
-                const int idx = next_idx < params.num_tiles ? next_idx : -1;
+            Tile w, wn;
+            // decode tile index idx (or the end marker) and hand the record to the other warps
+            auto publish = [&](int round, int idx, Tile& t) {
                 const int ts = round % kSchedDepth;
+                if (idx < params.num_tiles) decode_tile(params, idx, t);
+                else t.mblock = -1;
                 mbar_wait(bar(L::kBarTileEmpty + ts), ((round / kSchedDepth) & 1) ^ 1u, status, 21);
-                asm volatile("st.shared.s32 [%0], %1;" ::"r"(smem_base + L::kTileRing + ts * 4), "r"(idx) : "memory");
+                tile_store<L>(smem_base, ts, t);
                 mbar_arrive(bar(L::kBarTileFull + ts));
-                if (idx < 0) break;
-                // prefetch the next index; the atomic's latency hides behind this tile's TMA issue
-                next_idx = int(gridDim.x) + atomicAdd(params.sched, 1);
-                decode_tile(params, idx, w);
-                // Q_t of the new work tile goes out as soon as M-tile t of the previous one has issued
-                // its last S (QEmpty) — independently for the two tiles, and interleaved with the K/V
-                // stages below, so the tile that finishes first restarts without waiting for the other.
-                bool q_pending[2] = {w.nblk[0] > 0, w.nblk[1] > 0};
-                auto try_q = [&](int t, bool block) {
-                    if (!q_pending[t]) return;
-                    if (block) mbar_wait(bar(L::kBarQEmpty + t), qe_phase[t] ^ 1u, status, 10);
-                    else if (!mbar_test_wait(bar(L::kBarQEmpty + t), qe_phase[t] ^ 1u)) return;
-                    qe_phase[t] ^= 1u;
-                    const uint32_t qbar = bar(L::kBarQFull + t);
-                    mbar_arrive_expect_tx(qbar, params.q_tile_bytes);
-                    for (int pn = 0; pn < kPanels; ++pn)
-                        tma_load_5d(smem_base + (t ? L::kQ1 : L::kQ0) + pn * kPanelBytes,
-                                    &params.tm_q, qbar, pn * 64, w.pos0[t], w.g_coord, w.kv_head, w.b);
-                    q_pending[t] = false;
+            };
+            publish(0, blockIdx.x, w);  // first tile: no atomic
+            // The index after that is always in flight: the atomic's round trip (about 1000 cycles
+            // with every CTA on one counter) must not sit between two work tiles.
+            int next_idx = int(gridDim.x) + atomicAdd(params.sched, 1);
+            for (int round = 0; w.mblock >= 0; ++round) {
+                bool next_published = false;
+                // The next tile is decoded and published while this tile's stages wait for ring
+                // slots: the Q loader needs it before this tile ends, and a consumer that finishes
+                // early finds it ready.
+                auto publish_next = [&]() {
+                    publish(round + 1, next_idx, wn);
+                    next_published = true;
+                    if (wn.mblock >= 0) next_idx = int(gridDim.x) + atomicAdd(params.sched, 1);
                 };
                 tr.ev(1);
                 // Ring stages of two 64-key half tiles, in the order the MMA issuers consume them
@@ -212,15 +239,6 @@ fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
                     const CUtensorMap* tm1 = (i == nh - 1) ? &params.tm_v : &params.tm_k;
                     const int h0 = (i == 0) ? 0 : i - 1;
                     const int h1 = (i == nh - 1) ? nh - 1 : i + 1;
-                    // While a Q tile is still pending the wait for a ring slot must not block: the slot
-                    // may only be released by MMAs that need that Q.
-                    while (q_pending[0] || q_pending[1]) {
-                        try_q(0, false);
-                        try_q(1, false);
-                        if (mbar_test_wait(bar(L::kBarKVEmpty + slot), phase ^ 1u)) break;
-                        __nanosleep(64);
-                        if (*reinterpret_cast<volatile unsigned int*>(status) != 0u) break;  // watchdog elsewhere
-                    }
                     mbar_wait(bar(L::kBarKVEmpty + slot), phase ^ 1u, status, 1);
                     const uint32_t fb = bar(L::kBarKVFull + slot);
                     mbar_arrive_expect_tx(fb, 2 * kHalfBytes);
@@ -230,9 +248,38 @@ fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
                     for (int pn = 0; pn < kPanels; ++pn)
                         tma_load_4d(dst + kHalfBytes + pn * kHalfPanel, tm1, fb, pn * 64, h1 * 64, w.kv_head, w.b);
                     if (++slot == kStages) { slot = 0; phase ^= 1u; }
+                    tr.ev(6);
+                    if (i == 1) publish_next();
                 }
-                try_q(0, true);
-                try_q(1, true);
+                if (!next_published) publish_next();
+                w = wn;
+            }
+        } else if (warp == kQWarp && elected) {
+            // =========================== Q loader ===========================
+            // Q_t of a work tile goes out as soon as M-tile t of the previous one has issued its last
+            // S (QEmpty) — independently for the two M-tiles and of the K/V ring, so the tile that
+            // finishes first restarts without waiting for the other.
+            uint32_t qe_phase0 = 0, qe_phase1 = 0;
+            Tile w;
+            TileConsumer<L> sched(smem_base, status);
+            while (sched.next(w, true)) {
+                bool pend0 = w.nblk[0] > 0, pend1 = w.nblk[1] > 0;
+                auto load_q = [&](int t) {
+                    const uint32_t qbar = bar(L::kBarQFull + t);
+                    mbar_arrive_expect_tx(qbar, params.q_tile_bytes);
+                    for (int pn = 0; pn < kPanels; ++pn)
+                        tma_load_5d(smem_base + (t ? L::kQ1 : L::kQ0) + pn * kPanelBytes,
+                                    &params.tm_q, qbar, pn * 64, (t ? w.pos0[1] : w.pos0[0]), w.g_coord, w.kv_head, w.b);
+                };
+                for (uint32_t spins = 0; pend0 || pend1;) {
+                    if (pend0 && mbar_try_wait(bar(L::kBarQEmpty + 0), qe_phase0 ^ 1u)) {
+                        qe_phase0 ^= 1u; pend0 = false; load_q(0);
+                    }
+                    if (pend1 && mbar_try_wait(bar(L::kBarQEmpty + 1), qe_phase1 ^ 1u)) {
+                        qe_phase1 ^= 1u; pend1 = false; load_q(1);
+                    }
+                    if ((++spins & 0xffu) == 0 && *reinterpret_cast<volatile unsigned int*>(status) != 0u) break;
+                }
             }
         } else if ((warp == kMmaWarp || warp == kMmaWarp + 1) && elected) {
             // =========================== MMA issuer ===========================
@@ -281,16 +328,22 @@ fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
             uint32_t q_phase = 0, oe_phase = 0;
             uint32_t blk_base = 0;  // KV blocks of earlier work tiles, mod 2 (P barrier parity)
             Tile w;
+            Tile wn;
             TileConsumer<L> sched(smem_base, status);
-            while (sched.next(params, w, true)) {
-                if (w.nmax == 0) continue;
+            // The next tile's record is published one work tile ahead; it is read in front of the
+            // wait for the last P of this tile (idle time) so that nothing but the Q/K waits sits
+            // between the last P·V of one tile and the first S of the next.
+            bool have = sched.next(w, true);
+            while (have) {
+                bool fetched = false, have_next = false;
+                if (w.nmax > 0) {
                 auto ring = [&](int it, int& s_, uint32_t& ph_) {
                     const int x = slot0 + it;
                     const int q = x / kStages;
                     s_ = x - q * kStages;
                     ph_ = phase0 ^ static_cast<uint32_t>(q & 1);
                 };
-                const int nh = 2 * w.nblk[t];
+                const int nh = 2 * (t ? w.nblk[1] : w.nblk[0]);
                 const int nhmax = 2 * w.nmax;
                 // wait for ring stage i of this work tile; returns the index of its first half slot
                 auto acquire = [&](int i, uint32_t code) {
@@ -314,6 +367,10 @@ fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
                     int st = 0;  // stage holding V(h): stage h+1 {V(h), K(h+2)}, or the last one {V(nh-2), V(nh-1)}
                     for (int h = 0; h < nh; ++h) {
                         const int b = h & 1;
+                        if (h == nh - 1) {
+                            have_next = sched.next(wn, true);
+                            fetched = true;
+                        }
                         mbar_wait(bar(L::kBarPFull + 2 * t + b), (blk_base + (h >> 1)) & 1u, status, 5);
                         if (h == 0) {  // O_t of the previous work tile must have been drained
                             mbar_wait(bar(L::kBarOEmpty + t), oe_phase ^ 1u, status, 11);
@@ -336,17 +393,22 @@ fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
                     }
                 }
                 // stages only the other (longer) M-tile uses: stay in lockstep with the ring
+                tr.ev(23);
                 for (int i = (nh > 0 ? nh + 1 : 0); i < nhmax; ++i) {
                     const int sl = acquire(i, 16);
                     mbar_arrive(bar(L::kBarKVEmpty + sl));
                 }
-                blk_base += static_cast<uint32_t>(w.nblk[t]);
+                blk_base += static_cast<uint32_t>((t ? w.nblk[1] : w.nblk[0]));
                 {
                     const int x = slot0 + 2 * w.nmax;  // nhmax stages
                     const int q = x / kStages;
                     slot0 = x - q * kStages;
                     phase0 ^= static_cast<uint32_t>(q & 1);
                 }
+                }  // w.nmax > 0
+                if (!fetched) have_next = sched.next(wn, true);
+                w = wn;
+                have = have_next;
             }
         }
     } else if (warp >= kEpiWarp0) {
@@ -358,14 +420,14 @@ fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
         uint32_t rs_phase[2] = {0, 0}, of_phase[2] = {0, 0};
         Tile w;
         TileConsumer<L> sched(smem_base, status);
-        while (sched.next(params, w, lane == 0)) {
+        while (sched.next(w, lane == 0)) {
             // O / l -> T -> global (row-contiguous 16 B stores)
 #pragma unroll
             for (int t = 0; t < 2; ++t) {
-                if (w.pos0[t] >= params.seqlen_q) continue;
-                const int n = w.nblk[t];
+                if ((t ? w.pos0[1] : w.pos0[0]) >= params.seqlen_q) continue;
+                const int n = (t ? w.nblk[1] : w.nblk[0]);
                 const int g = r / P;
-                const int pos = w.pos0[t] + (r - g * P);
+                const int pos = (t ? w.pos0[1] : w.pos0[0]) + (r - g * P);
                 const bool row_valid = (g < params.pack_g) && (pos < params.seqlen_q);
                 const int head = packed ? w.hu * params.group + g : w.hu;
                 uint8_t* orow = reinterpret_cast<uint8_t*>(params.o) +
@@ -437,10 +499,10 @@ fa_fwd_sm100_v5(const __grid_constant__ FwdParams params) {
         uint32_t blk_base = 0;  // KV blocks of earlier work tiles, mod 2 (S barrier parity)
         Tile w;
         TileConsumer<L> sched(smem_base, status);
-        while (sched.next(params, w, lane == 0)) {
-            const int n = w.nblk[t];
+        while (sched.next(w, lane == 0)) {
+            const int n = (t ? w.nblk[1] : w.nblk[0]);
             if (n == 0) continue;
-            const int my_pos0 = w.pos0[t];
+            const int my_pos0 = (t ? w.pos0[1] : w.pos0[0]);
             const int g = r / P;
             const int pos = my_pos0 + (r - g * P);
             int row_limit = params.seqlen_k - 1;  // last visible column
