@@ -340,7 +340,7 @@ def run_ours(args, w):
             "pct_of_nominal_2250": 100.0 * (value / world) / 2250.0,
             "roofline": {"bound": "tensor", "achieved": kernel_tflops, "peak": peak, "unit": "TFLOP/s",
                          "frac": kernel_tflops / peak, "traffic": traffic, "peak_source": peak_src,
-                         "kernel": "fa100::v5::fa_fwd_sm100_v5<128,bf16,10 half-tile stages,emu 3/8>", "kernel_ms": kernel_ms},
+                         "kernel": "fa100::v5::fa_fwd_sm100_v5<D=128,bf16,5 ring stages x 2 half tiles,emu 3/8>", "kernel_ms": kernel_ms},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps, "result_matches_device_run": bool(e2e_ok)},
             "gpu_launches": int(launches),
