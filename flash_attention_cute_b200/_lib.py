@@ -42,6 +42,8 @@ STATUS_NAMES = {
 # Every symbol include/fa_sm100.h declares (tests check the library exports all of them).
 EXPORTED_SYMBOLS = (
     "fa_sm100_fwd",
+    "fa_sm100_fwd_decode",
+    "fa_sm100_decode_plan",
     "fa_sm100_last_error",
     "fa_sm100_check_device",
     "fa_sm100_launch_count",
@@ -113,6 +115,10 @@ def load() -> ctypes.CDLL:
         lib.fa_sm100_build_info.restype = c_char_p
         lib.fa_sm100_plan.argtypes = [POINTER(FwdParams)] + [POINTER(c_int32)] * 4
         lib.fa_sm100_plan.restype = c_int32
+        lib.fa_sm100_decode_plan.argtypes = [POINTER(FwdParams), POINTER(c_int32), POINTER(c_int32), POINTER(c_int64)]
+        lib.fa_sm100_decode_plan.restype = c_int32
+        lib.fa_sm100_fwd_decode.argtypes = [POINTER(FwdParams), c_void_p, c_int64, c_void_p]
+        lib.fa_sm100_fwd_decode.restype = c_int32
         lib.fa_sm100_selftest_umma.argtypes = [
             c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
             c_int32, c_int32, c_float, c_uint32, c_uint32, c_int32, c_void_p,

@@ -19,6 +19,7 @@
 #include "fa_sm100_fwd4.cuh"
 #include "fa_sm100_fwd5.cuh"
 #include "fa_sm100_fwd6.cuh"
+#include "fa_sm100_decode.cuh"
 
 namespace {
 
@@ -524,6 +525,149 @@ extern "C" int fa_sm100_fwd(const fa_sm100_fwd_params* p, void* stream) {
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(FA_SM100_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(e));
+    g_launches.fetch_add(1);
+    return FA_SM100_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Split-KV decode (Sq == 1): fa_sm100_decode.cuh
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+struct DecodePlan {
+    int kd, group, units, nsplit, chunk;
+    int64_t counters_bytes, ml_bytes, o_bytes;
+};
+
+int decode_plan(const fa_sm100_fwd_params* p, int num_sms, DecodePlan* dp) {
+    Plan plan;
+    int rc = validate_and_plan(p, &plan);
+    if (rc) return rc;
+    if (p->seqlen_q != 1)
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT, "decode kernel needs seqlen_q == 1 (got %lld)",
+                    (long long)p->seqlen_q);
+    dp->group = int(p->heads_q / p->heads_kv);
+    if (dp->group > fa100::decode::kRows)
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT,
+                    "decode kernel packs at most %d q heads per kv head (got %d); use fa_sm100_fwd",
+                    fa100::decode::kRows, dp->group);
+    if (!(p->softmax_scale > 0.f))
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT, "decode kernel needs softmax_scale > 0");
+    if (p->seqlen_kv > 0x7fffffffll / 2 || p->batch * p->heads_kv > (1ll << 24))
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT, "problem size out of range");
+    dp->kd = plan.kd;
+    dp->units = int(p->batch * p->heads_kv);
+    // One wave: two CTAs per SM.  A split shorter than 256 keys is not worth its merge.
+    const int tile = fa100::decode::kWarps * fa100::decode::kTileKeys;
+    const int slots = 2 * (num_sms > 0 ? num_sms : 148);
+    int64_t nsplit = slots / dp->units;
+    const int64_t max_split = p->seqlen_kv / 256;
+    if (nsplit > max_split) nsplit = max_split;
+    if (nsplit < 1) nsplit = 1;
+    int64_t chunk = (p->seqlen_kv + nsplit - 1) / nsplit;
+    chunk = (chunk + tile - 1) / tile * tile;
+    nsplit = (p->seqlen_kv + chunk - 1) / chunk;
+    dp->nsplit = int(nsplit);
+    dp->chunk = int(chunk);
+    dp->counters_bytes = nsplit > 1 ? (int64_t(dp->units) * 4 + 255) / 256 * 256 : 0;
+    dp->ml_bytes = nsplit > 1 ? int64_t(dp->units) * nsplit * fa100::decode::kRows * 2 * 4 : 0;
+    dp->o_bytes = nsplit > 1 ? int64_t(dp->units) * nsplit * fa100::decode::kRows * dp->kd * 4 : 0;
+    return FA_SM100_OK;
+}
+
+using DecodeFn = void (*)(const fa100::decode::DecodeParams);
+struct DecodeVariant {
+    DecodeFn fn;
+    int smem_bytes;
+    std::once_flag attr_once[kMaxDevices];
+};
+template <int kD, bool kBf16>
+DecodeVariant* decode_variant() {
+    static DecodeVariant v{fa100::decode::fa_decode_sm100<kD, kBf16>, fa100::decode::Smem<kD>::kTotal};
+    return &v;
+}
+
+}  // namespace
+
+extern "C" int fa_sm100_decode_plan(const fa_sm100_fwd_params* p, int32_t* nsplit, int32_t* chunk,
+                                    int64_t* workspace_bytes) {
+    DecodePlan dp;
+    int num_sms = 148;
+    if (p) {
+        DeviceState* st = (p->device >= 0 && p->device < kMaxDevices) ? &g_dev[p->device] : nullptr;
+        if (st && st->num_sms > 0) num_sms = st->num_sms;  // only if the device was initialised already
+    }
+    int rc = decode_plan(p, num_sms, &dp);
+    if (rc) return rc;
+    if (nsplit) *nsplit = dp.nsplit;
+    if (chunk) *chunk = dp.chunk;
+    if (workspace_bytes) *workspace_bytes = dp.counters_bytes + dp.ml_bytes + dp.o_bytes;
+    return FA_SM100_OK;
+}
+
+extern "C" int fa_sm100_fwd_decode(const fa_sm100_fwd_params* p, void* workspace,
+                                   int64_t workspace_bytes, void* stream) {
+    if (!p) return fail(FA_SM100_ERR_INVALID_ARGUMENT, "params is NULL");
+    DeviceState* st = device_state(p->device);
+    if (!st) return fail(FA_SM100_ERR_INVALID_ARGUMENT, "bad device ordinal %d", p->device);
+    if (st->error) return fail(st->error, "device init failed: %s", st->msg);
+    if (st->cc_major != 10)
+        return fail(FA_SM100_ERR_UNSUPPORTED_DEVICE,
+                    "fa_sm100 needs an sm_100 (B200) GPU; device %d is sm_%d%d — there is no fallback",
+                    p->device, st->cc_major, st->cc_minor);
+    DecodePlan dp;
+    int rc = decode_plan(p, st->num_sms, &dp);
+    if (rc) return rc;
+    const int64_t need = dp.counters_bytes + dp.ml_bytes + dp.o_bytes;
+    if (dp.nsplit > 1) {
+        if (!workspace || workspace_bytes < need)
+            return fail(FA_SM100_ERR_INVALID_ARGUMENT,
+                        "decode workspace too small: need %lld bytes (fa_sm100_decode_plan), got %lld",
+                        (long long)need, (long long)workspace_bytes);
+        if (reinterpret_cast<uintptr_t>(workspace) & 255u)
+            return fail(FA_SM100_ERR_INVALID_ARGUMENT, "decode workspace must be 256-byte aligned");
+    }
+
+    int prev = 0;
+    cudaGetDevice(&prev);
+    if (prev != p->device) cudaSetDevice(p->device);
+    struct Restore {
+        int prev, cur;
+        ~Restore() { if (prev != cur) cudaSetDevice(prev); }
+    } restore{prev, p->device};
+
+    const bool bf16 = p->dtype == FA_SM100_BF16;
+    DecodeVariant* var = dp.kd == 128 ? (bf16 ? decode_variant<128, true>() : decode_variant<128, false>())
+                                      : (bf16 ? decode_variant<64, true>() : decode_variant<64, false>());
+    cudaError_t attr_err = cudaSuccess;
+    std::call_once(var->attr_once[p->device], [&] {
+        attr_err = cudaFuncSetAttribute(reinterpret_cast<const void*>(var->fn),
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, var->smem_bytes);
+    });
+    if (attr_err != cudaSuccess)
+        return fail(FA_SM100_ERR_CUDA, "cudaFuncSetAttribute(decode): %s", cudaGetErrorString(attr_err));
+
+    fa100::decode::DecodeParams kp;
+    memset(&kp, 0, sizeof(kp));
+    kp.q = p->q; kp.k = p->k; kp.v = p->v; kp.o = p->o;
+    kp.batch = int(p->batch); kp.heads_kv = int(p->heads_kv); kp.group = dp.group;
+    kp.seqlen_k = int(p->seqlen_kv); kp.headdim = int(p->headdim);
+    kp.q_sb = p->q_strides[0]; kp.q_sh = p->q_strides[1];
+    kp.k_sb = p->k_strides[0]; kp.k_sh = p->k_strides[1]; kp.k_ss = p->k_strides[2];
+    kp.v_sb = p->v_strides[0]; kp.v_sh = p->v_strides[1]; kp.v_ss = p->v_strides[2];
+    kp.o_sb = p->o_strides[0]; kp.o_sh = p->o_strides[1];
+    kp.scale_log2 = p->softmax_scale * 1.4426950408889634f;
+    kp.nsplit = dp.nsplit; kp.chunk = dp.chunk;
+    if (dp.nsplit > 1) {
+        uint8_t* ws = static_cast<uint8_t*>(workspace);
+        kp.counters = reinterpret_cast<int*>(ws);
+        kp.part_ml = reinterpret_cast<float*>(ws + dp.counters_bytes);
+        kp.part_o = reinterpret_cast<float*>(ws + dp.counters_bytes + dp.ml_bytes);
+    }
+    var->fn<<<dim3(dp.units * dp.nsplit), dim3(fa100::decode::kThreads), var->smem_bytes,
+              static_cast<cudaStream_t>(stream)>>>(kp);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(FA_SM100_ERR_CUDA, "decode kernel launch: %s", cudaGetErrorString(e));
     g_launches.fetch_add(1);
     return FA_SM100_OK;
 }

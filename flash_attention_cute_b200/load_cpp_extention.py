@@ -18,6 +18,10 @@ from . import _lib
 _DTYPES = {torch.float16: _lib.FA_SM100_FP16, torch.bfloat16: _lib.FA_SM100_BF16}
 
 
+FLAG_NO_DECODE = 8       # include/fa_sm100.h: FA_SM100_FLAG_NO_DECODE
+DECODE_MAX_GROUP = 16    # csrc/fa_sm100_decode.cuh: kRows
+
+
 def _check(cond: bool, msg: str) -> None:
     if not cond:
         raise RuntimeError(msg)
@@ -57,6 +61,7 @@ class FlashAttentionExtension:
 
     def __init__(self) -> None:
         self._lib = _lib.load()
+        self._workspaces = {}
 
     def flash_attention_fwd(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor,
                             softmax_scale: float, causal: bool, flags: int = 0) -> torch.Tensor:
@@ -96,9 +101,44 @@ class FlashAttentionExtension:
 
         params = fill_params(q, k, v, o, softmax_scale, causal, flags)
         stream = torch.cuda.current_stream(q.device).cuda_stream
-        rc = self._lib.fa_sm100_fwd(ctypes.byref(params), ctypes.c_void_p(stream))
+        # Sq == 1 (the reference's packing branch, csrc/flash_attention_api.cpp:72-83) goes to the
+        # split-KV decode kernel whenever it applies: G <= 16 q heads per kv head, positive scale.
+        if (q.size(2) == 1 and q.size(1) // k.size(1) <= DECODE_MAX_GROUP and softmax_scale > 0
+                and not (flags & FLAG_NO_DECODE)):
+            ws = self._decode_workspace(params, q.device, stream)
+            rc = self._lib.fa_sm100_fwd_decode(ctypes.byref(params),
+                                               ctypes.c_void_p(ws.data_ptr() if ws is not None else 0),
+                                               ctypes.c_int64(ws.numel() if ws is not None else 0),
+                                               ctypes.c_void_p(stream))
+        else:
+            rc = self._lib.fa_sm100_fwd(ctypes.byref(params), ctypes.c_void_p(stream))
         _lib.raise_for_status(rc)
         return o
+
+    def decode_plan(self, q, k, v) -> dict:
+        """Split the decode kernel would use for these shapes (no launch; works without a GPU)."""
+        params = fill_params(q, k, v, q, 1.0, False, 0)
+        nsplit, chunk, nbytes = ctypes.c_int32(), ctypes.c_int32(), ctypes.c_int64()
+        rc = self._lib.fa_sm100_decode_plan(ctypes.byref(params), ctypes.byref(nsplit), ctypes.byref(chunk),
+                                            ctypes.byref(nbytes))
+        _lib.raise_for_status(rc)
+        return {"nsplit": nsplit.value, "chunk": chunk.value, "workspace_bytes": nbytes.value}
+
+    def _decode_workspace(self, params, device, stream):
+        """Grow-only workspace per (device, stream): launches on one stream are ordered, so they can
+        share it; its counter words start zeroed and every launch leaves them zeroed
+        (include/fa_sm100.h: fa_sm100_fwd_decode)."""
+        nbytes = ctypes.c_int64()
+        rc = self._lib.fa_sm100_decode_plan(ctypes.byref(params), None, None, ctypes.byref(nbytes))
+        _lib.raise_for_status(rc)
+        if nbytes.value == 0:
+            return None
+        key = (device.index, stream)
+        ws = self._workspaces.get(key)
+        if ws is None or ws.numel() < nbytes.value:
+            ws = torch.zeros(max(nbytes.value, 1 << 22), dtype=torch.uint8, device=device)
+            self._workspaces[key] = ws
+        return ws
 
     def plan(self, q, k, v, causal: bool = False, flags: int = 0) -> dict:
         """Describe the launch fa_sm100_fwd would do (no launch; works without a GPU)."""

@@ -57,6 +57,8 @@ enum fa_sm100_status {
 #define FA_SM100_FLAG_NO_PACK_GQA 1u   /* do not pack the q heads of a kv group into one M tile */
 #define FA_SM100_FLAG_FORCE_PACK_GQA 2u /* pack whenever Hq/Hkv > 1 (default: heuristic)        */
 #define FA_SM100_FLAG_KERNEL_V1 4u      /* debug: first-generation (non-persistent) kernel       */
+#define FA_SM100_FLAG_NO_DECODE 8u      /* operator-level routing hint: keep seqlen_q == 1 on
+                                           fa_sm100_fwd instead of fa_sm100_fwd_decode            */
 /* Tuning bits (honoured by FA_SM100_TUNE builds, ignored otherwise):
  *   bits 8-11  1 + number of exp2 evaluations per 4 element pairs moved to the FMA pipe (0 = default)
  *   bits 12-13 P hand-off split: 0 = default, 1 = 64 keys first, 2 = 96, 3 = no split
@@ -91,6 +93,25 @@ typedef struct fa_sm100_fwd_params {
 /* Launch the forward kernel on `stream` (a cudaStream_t passed as void*; NULL = default stream).
  * Returns fa_sm100_status. */
 int fa_sm100_fwd(const fa_sm100_fwd_params* params, void* stream);
+
+/* ---- Decode (seqlen_q == 1) with split-KV --------------------------------------------------------
+ * Replaces the reference's Sq == 1 branch, which packs the q heads of a kv group into one M tile
+ * and runs the prefill kernel with one CTA per (batch, kv-head)
+ * (csrc/flash_attention_api.cpp:72-83, 128-133; "Flash Decoding" is a TODO at README.md:20).
+ * Same params struct and semantics as fa_sm100_fwd (causal is irrelevant: with bottom-right
+ * alignment the single query row sees every key); requires seqlen_q == 1, Hq/Hkv <= 16 and
+ * softmax_scale > 0 — anything else is FA_SM100_ERR_INVALID_ARGUMENT and belongs to fa_sm100_fwd.
+ * The K/V sequence of each (batch, kv-head) unit is cut into `nsplit` chunks, one CTA each; the
+ * last CTA of a unit merges the partial (max, sum, O) triples, so it is still ONE launch.
+ *
+ * fa_sm100_decode_plan reports the split the library would use and the workspace it needs
+ * (0 bytes when nsplit == 1).  The caller owns the workspace: 256-byte aligned device memory whose
+ * first ceil(4·B·Hkv / 256)·256 bytes are ZERO before the first launch that uses it; every launch
+ * leaves them zero again, so one buffer serves all stream-ordered launches. */
+int fa_sm100_decode_plan(const fa_sm100_fwd_params* params, int32_t* nsplit, int32_t* chunk_keys,
+                         int64_t* workspace_bytes);
+int fa_sm100_fwd_decode(const fa_sm100_fwd_params* params, void* workspace, int64_t workspace_bytes,
+                        void* stream);
 
 /* Thread-local, NUL-terminated description of the last non-zero status on this thread. */
 const char* fa_sm100_last_error(void);

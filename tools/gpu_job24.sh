@@ -1,0 +1,4 @@
+#!/usr/bin/env bash
+set -u
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_decode.py tests/test_parity.py -m gpu -x -q -k "decode" > gpurun_out/pytest_decode.log 2>&1; echo "pytest rc=$?"; tail -25 gpurun_out/pytest_decode.log
