@@ -334,23 +334,78 @@ fa_decode_sm100(const DecodeParams p) {
     __syncthreads();
     if (threadIdx.x == 0) *flag = (atomicAdd(p.counters + unit, 1) == p.nsplit - 1);
     __syncthreads();
-    if (!*flag) return;
+    const bool last = *flag != 0;
+    __syncthreads();  // the merge below reuses the shared memory the flag lives in
+    if (!last) return;
     __threadfence();
+    // Every load below is independent of the previous one (the partials come from L2 at some
+    // 600 ns a round trip: a serial loop over the splits would cost more than the whole K/V stream).
+    // 1. all (m, l) pairs of the unit -> shared memory, coalesced float4 loads
     const int64_t ubase = static_cast<int64_t>(unit) * p.nsplit * kRows;
-    for (int idx = threadIdx.x; idx < G * kD; idx += kThreads) {
-        const int row = idx / kD, d = idx - row * kD;
-        if (d >= D) continue;
+    float* sm_ml = reinterpret_cast<float*>(smem);  // [nsplit][kRows][2], later (f, -) in place
+    {
+        const float4* src = reinterpret_cast<const float4*>(p.part_ml + ubase * 2);
+        const int n4 = p.nsplit * kRows * 2 / 4;
+#pragma unroll 4
+        for (int i = threadIdx.x; i < n4; i += kThreads)
+            reinterpret_cast<float4*>(sm_ml)[i] = __ldcg(src + i);
+    }
+    __syncthreads();
+    // 2. per row: global max, total sum, and the weight of every split (8 lanes per row)
+    {
+        const int row = threadIdx.x >> 3, part = threadIdx.x & 7;
         float m = kNegBig;
-        for (int sp = 0; sp < p.nsplit; ++sp) m = fmaxf(m, __ldcg(p.part_ml + (ubase + sp * kRows + row) * 2));
-        float acc = 0.f, l = 0.f;
-        for (int sp = 0; sp < p.nsplit; ++sp) {
-            const int64_t r = ubase + sp * kRows + row;
-            const float f = fast_exp2(__ldcg(p.part_ml + r * 2) - m);
-            acc = fmaf(__ldcg(p.part_o + r * kD + d), f, acc);
-            l = fmaf(__ldcg(p.part_ml + r * 2 + 1), f, l);
-        }
+        for (int sp = part; sp < p.nsplit; sp += 8) m = fmaxf(m, sm_ml[(sp * kRows + row) * 2]);
+        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
+        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 4));
+        float l = 0.f;
+        for (int sp = part; sp < p.nsplit; sp += 8)
+            l = fmaf(sm_ml[(sp * kRows + row) * 2 + 1], fast_exp2(sm_ml[(sp * kRows + row) * 2] - m), l);
+        l += __shfl_xor_sync(0xffffffffu, l, 1);
+        l += __shfl_xor_sync(0xffffffffu, l, 2);
+        l += __shfl_xor_sync(0xffffffffu, l, 4);
         const float inv = l > 0.f ? __frcp_rn(l) : 0.f;
-        store_out<kBf16>(p.o, b * p.o_sb + (static_cast<int64_t>(kvh) * G + row) * p.o_sh + d, acc * inv);
+        for (int sp = part; sp < p.nsplit; sp += 8)
+            sm_ml[(sp * kRows + row) * 2] = fast_exp2(sm_ml[(sp * kRows + row) * 2] - m) * inv;
+    }
+    __syncthreads();
+    // 3. O[row][d..d+3] = sum over splits of weight * partial O, float4 per thread, 8 loads in flight
+    for (int idx = threadIdx.x; idx < G * (kD / 4); idx += kThreads) {
+        const int row = idx / (kD / 4), d = (idx - row * (kD / 4)) * 4;
+        if (d >= D) continue;
+        const float4* src = reinterpret_cast<const float4*>(p.part_o + (ubase + row) * kD + d);
+        const int64_t step = static_cast<int64_t>(kRows) * kD / 4;  // float4s between splits
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        int sp = 0;
+        for (; sp + 8 <= p.nsplit; sp += 8) {
+            float4 x[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) x[u] = __ldcg(src + (sp + u) * step);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const float f = sm_ml[((sp + u) * kRows + row) * 2];
+                acc.x = fmaf(x[u].x, f, acc.x); acc.y = fmaf(x[u].y, f, acc.y);
+                acc.z = fmaf(x[u].z, f, acc.z); acc.w = fmaf(x[u].w, f, acc.w);
+            }
+        }
+        {
+            float4 x[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+                x[u] = sp + u < p.nsplit ? __ldcg(src + (sp + u) * step) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const float f = sp + u < p.nsplit ? sm_ml[((sp + u) * kRows + row) * 2] : 0.f;
+                acc.x = fmaf(x[u].x, f, acc.x); acc.y = fmaf(x[u].y, f, acc.y);
+                acc.z = fmaf(x[u].z, f, acc.z); acc.w = fmaf(x[u].w, f, acc.w);
+            }
+        }
+        const int64_t o_idx = b * p.o_sb + (static_cast<int64_t>(kvh) * G + row) * p.o_sh + d;
+        uint2 packed;
+        packed.x = pack2<kBf16>(acc.x, acc.y);
+        packed.y = pack2<kBf16>(acc.z, acc.w);
+        *reinterpret_cast<uint2*>(reinterpret_cast<T*>(p.o) + o_idx) = packed;  // D % 8 == 0, 16 B-aligned rows
     }
     if (threadIdx.x == 0) p.counters[unit] = 0;  // re-arm for the next launch on this workspace
 }
