@@ -150,23 +150,6 @@ fa_decode_sm100(const DecodeParams p) {
     const T* vbase = reinterpret_cast<const T*>(p.v) + b * p.v_sb + kvh * p.v_sh;
     const uint32_t ring = smem_addr(smem) + warp * L::kWarpBytes;
 
-    // ---- Q fragments (A operand, rows = heads of the group), straight from global ----
-    uint32_t qa[kKSteps][4];
-    {
-        const T* qbase = reinterpret_cast<const T*>(p.q) + b * p.q_sb + static_cast<int64_t>(kvh) * G * p.q_sh;
-        const int r0 = lane >> 2, c0 = (lane & 3) * 2;
-#pragma unroll
-        for (int ks = 0; ks < kKSteps; ++ks) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int row = r0 + (i & 1) * 8, col = ks * 16 + c0 + (i >> 1) * 8;
-                uint32_t x = 0;
-                if (row < G && col < D) x = *reinterpret_cast<const uint32_t*>(qbase + row * p.q_sh + col);
-                qa[ks][i] = x;
-            }
-        }
-    }
-
     // ---- per-warp cp.async ring ----
     auto issue_tile = [&](int t) {  // t: tile index inside the chunk (this warp's), may be >= ntiles
         if (t < ntiles) {
@@ -195,6 +178,25 @@ fa_decode_sm100(const DecodeParams p) {
 
     issue_tile(warp);
     issue_tile(warp + kWarps);
+
+    // ---- Q fragments (A operand, rows = heads of the group), straight from global, under the
+    //      latency of the first two K/V tiles ----
+    uint32_t qa[kKSteps][4];
+    {
+        const T* qbase = reinterpret_cast<const T*>(p.q) + b * p.q_sb + static_cast<int64_t>(kvh) * G * p.q_sh;
+        const int r0 = lane >> 2, c0 = (lane & 3) * 2;
+#pragma unroll
+        for (int ks = 0; ks < kKSteps; ++ks) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int row = r0 + (i & 1) * 8, col = ks * 16 + c0 + (i >> 1) * 8;
+                uint32_t x = 0;
+                if (row < G && col < D) x = *reinterpret_cast<const uint32_t*>(qbase + row * p.q_sh + col);
+                qa[ks][i] = x;
+            }
+        }
+    }
+
     for (int t = warp; t < ntiles; t += kWarps) {
         issue_tile(t + 2 * kWarps);
         cp_async_wait<2>();
