@@ -21,7 +21,7 @@ LIB = PKG / "libfa_sm100.so"
 STAMP = PKG / ".libfa_sm100.stamp"
 
 SOURCES = [CSRC / "fa_sm100_host.cu", CSRC / "fa_sm100_selftest.cu"]
-HEADERS = [CSRC / "fa_sm100_kernel.cuh", CSRC / "fa_sm100_fwd.cuh", CSRC / "fa_sm100_fwd4.cuh", CSRC / "fa_sm100_fwd5.cuh", CSRC / "fa_sm100_fwd6.cuh", CSRC / "fa_sm100_decode.cuh", CSRC / "fa_sm100_ptx.cuh",
+HEADERS = [CSRC / "fa_sm100_kernel.cuh", CSRC / "fa_sm100_fwd.cuh", CSRC / "fa_sm100_fwd4.cuh", CSRC / "fa_sm100_fwd5.cuh", CSRC / "fa_sm100_fwd6.cuh", CSRC / "fa_sm100_decode.cuh", CSRC / "fa_sm100_rope.cuh", CSRC / "fa_sm100_ptx.cuh",
            ROOT / "include" / "fa_sm100.h"]
 
 NVCC_FLAGS = [

@@ -44,6 +44,7 @@ EXPORTED_SYMBOLS = (
     "fa_sm100_fwd",
     "fa_sm100_fwd_decode",
     "fa_sm100_decode_plan",
+    "fa_sm100_rope",
     "fa_sm100_last_error",
     "fa_sm100_check_device",
     "fa_sm100_launch_count",
@@ -76,6 +77,31 @@ class FwdParams(Structure):
         ("dtype", c_int32),
         ("device", c_int32),
         ("flags", c_uint32),
+    ]
+
+
+class RopeParams(Structure):
+    """Mirror of fa_sm100_rope_params (include/fa_sm100.h)."""
+
+    _fields_ = [
+        ("q", c_void_p),
+        ("k", c_void_p),
+        ("q_out", c_void_p),
+        ("k_out", c_void_p),
+        ("cos", c_void_p),
+        ("sin", c_void_p),
+        ("batch", c_int64),
+        ("heads_q", c_int64),
+        ("heads_kv", c_int64),
+        ("seqlen", c_int64),
+        ("headdim", c_int64),
+        ("q_strides", c_int64 * 3),
+        ("k_strides", c_int64 * 3),
+        ("q_out_strides", c_int64 * 3),
+        ("k_out_strides", c_int64 * 3),
+        ("cos_sin_strides", c_int64 * 2),
+        ("dtype", c_int32),
+        ("device", c_int32),
     ]
 
 
@@ -119,6 +145,8 @@ def load() -> ctypes.CDLL:
         lib.fa_sm100_decode_plan.restype = c_int32
         lib.fa_sm100_fwd_decode.argtypes = [POINTER(FwdParams), c_void_p, c_int64, c_void_p]
         lib.fa_sm100_fwd_decode.restype = c_int32
+        lib.fa_sm100_rope.argtypes = [POINTER(RopeParams), c_void_p]
+        lib.fa_sm100_rope.restype = c_int32
         lib.fa_sm100_selftest_umma.argtypes = [
             c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
             c_int32, c_int32, c_float, c_uint32, c_uint32, c_int32, c_void_p,

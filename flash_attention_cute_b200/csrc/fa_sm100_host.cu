@@ -20,6 +20,7 @@
 #include "fa_sm100_fwd5.cuh"
 #include "fa_sm100_fwd6.cuh"
 #include "fa_sm100_decode.cuh"
+#include "fa_sm100_rope.cuh"
 
 namespace {
 
@@ -668,6 +669,83 @@ extern "C" int fa_sm100_fwd_decode(const fa_sm100_fwd_params* p, void* workspace
               static_cast<cudaStream_t>(stream)>>>(kp);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(FA_SM100_ERR_CUDA, "decode kernel launch: %s", cudaGetErrorString(e));
+    g_launches.fetch_add(1);
+    return FA_SM100_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Fused RoPE on q and k: fa_sm100_rope.cuh
+// ------------------------------------------------------------------------------------------------
+extern "C" int fa_sm100_rope(const fa_sm100_rope_params* p, void* stream) {
+    if (!p) return fail(FA_SM100_ERR_INVALID_ARGUMENT, "params is NULL");
+    if (!p->q || !p->k || !p->q_out || !p->k_out || !p->cos || !p->sin)
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT, "q, k, q_out, k_out, cos, sin must be non-NULL device pointers");
+    if (p->batch <= 0 || p->heads_q <= 0 || p->heads_kv <= 0 || p->seqlen <= 0 || p->headdim <= 0)
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT, "q, k must have at least one element");
+    if (p->headdim % 16 != 0 || p->headdim > 512)
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT, "rope: hidden dimension must be a multiple of 16 and <= 512");
+    if (p->dtype != FA_SM100_FP16 && p->dtype != FA_SM100_BF16)
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT, "q, k only support fp16 or bf16 data type");
+    auto aligned16 = [](const void* ptr) { return (reinterpret_cast<uintptr_t>(ptr) & 15u) == 0; };
+    if (!aligned16(p->q) || !aligned16(p->k) || !aligned16(p->q_out) || !aligned16(p->k_out) ||
+        !aligned16(p->cos) || !aligned16(p->sin))
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT, "rope: all pointers must be 16-byte aligned");
+    auto strides_ok = [](const int64_t* s, const int64_t* dims, int n) {
+        for (int i = 0; i < n; ++i)
+            if (dims[i] > 1 && (s[i] < 0 || s[i] % 8 != 0)) return false;
+        return true;
+    };
+    const int64_t qd[3] = {p->batch, p->heads_q, p->seqlen};
+    const int64_t kd[3] = {p->batch, p->heads_kv, p->seqlen};
+    const int64_t cd[2] = {p->batch, p->seqlen};
+    if (!strides_ok(p->q_strides, qd, 3) || !strides_ok(p->k_strides, kd, 3) ||
+        !strides_ok(p->q_out_strides, qd, 3) || !strides_ok(p->k_out_strides, kd, 3) ||
+        !strides_ok(p->cos_sin_strides, cd, 2))
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT,
+                    "rope: strides must be non-negative multiples of 8 elements (16 bytes)");
+    const long long total = (long long)p->batch * p->seqlen * (p->heads_q + p->heads_kv) * (p->headdim / 16);
+    if (p->seqlen > (1ll << 30) || p->heads_q + p->heads_kv > (1 << 20) || total > (1ll << 40))
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT, "problem size out of range");
+
+    DeviceState* st = device_state(p->device);
+    if (!st) return fail(FA_SM100_ERR_INVALID_ARGUMENT, "bad device ordinal %d", p->device);
+    if (st->error) return fail(st->error, "device init failed: %s", st->msg);
+    if (st->cc_major != 10)
+        return fail(FA_SM100_ERR_UNSUPPORTED_DEVICE,
+                    "fa_sm100 needs an sm_100 (B200) GPU; device %d is sm_%d%d — there is no fallback",
+                    p->device, st->cc_major, st->cc_minor);
+    int prev = 0;
+    cudaGetDevice(&prev);
+    if (prev != p->device) cudaSetDevice(p->device);
+    struct Restore {
+        int prev, cur;
+        ~Restore() { if (prev != cur) cudaSetDevice(prev); }
+    } restore{prev, p->device};
+
+    fa100::rope::RopeParams kp;
+    memset(&kp, 0, sizeof(kp));
+    kp.q = p->q; kp.k = p->k; kp.q_out = p->q_out; kp.k_out = p->k_out; kp.cos = p->cos; kp.sin = p->sin;
+    kp.batch = int(p->batch); kp.heads_q = int(p->heads_q); kp.heads_kv = int(p->heads_kv);
+    kp.seqlen = int(p->seqlen); kp.headdim = int(p->headdim);
+    for (int i = 0; i < 3; ++i) {
+        kp.q_s[i] = p->q_strides[i]; kp.k_s[i] = p->k_strides[i];
+        kp.qo_s[i] = p->q_out_strides[i]; kp.ko_s[i] = p->k_out_strides[i];
+    }
+    kp.cs_sb = p->batch > 1 ? p->cos_sin_strides[0] : 0;
+    kp.cs_ss = p->cos_sin_strides[1];
+    kp.total = total;
+    // enough CTAs to keep every SM's load queue full (8 per SM), grid-stride over the rest
+    long long blocks = (total + fa100::rope::kThreads - 1) / fa100::rope::kThreads;
+    const long long cap = 8ll * (st->num_sms > 0 ? st->num_sms : 148);
+    if (blocks > cap) blocks = cap;
+    if (p->dtype == FA_SM100_BF16)
+        fa100::rope::fa_rope_sm100<true><<<dim3((unsigned)blocks), dim3(fa100::rope::kThreads), 0,
+                                           static_cast<cudaStream_t>(stream)>>>(kp);
+    else
+        fa100::rope::fa_rope_sm100<false><<<dim3((unsigned)blocks), dim3(fa100::rope::kThreads), 0,
+                                            static_cast<cudaStream_t>(stream)>>>(kp);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(FA_SM100_ERR_CUDA, "rope kernel launch: %s", cudaGetErrorString(e));
     g_launches.fetch_add(1);
     return FA_SM100_OK;
 }

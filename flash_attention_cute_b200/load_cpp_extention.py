@@ -115,6 +115,48 @@ class FlashAttentionExtension:
         _lib.raise_for_status(rc)
         return o
 
+    def rope(self, q: torch.Tensor, k: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor):
+        """(q·cos + rotate_half(q)·sin, k·cos + rotate_half(k)·sin) in one kernel, bit-equal to the
+        reference expression (models/rope_attn_fwd.py:14-38).  q [B,Hq,S,D], k [B,Hkv,S,D] (strided
+        views welcome), cos / sin [B or 1, S, D].  Outputs keep the inputs' strides."""
+        _check(q.dim() == 4 and k.dim() == 4, "q, k must be 4-D [batch, heads, seq, dim]")
+        _check(cos.dim() == 3 and sin.dim() == 3 and cos.shape == sin.shape, "cos, sin must be 3-D [batch, seq, dim]")
+        _check(q.size(0) == k.size(0) and q.size(2) == k.size(2) and q.size(3) == k.size(3),
+               "q, k must agree in batch, sequence length and hidden dimension")
+        _check(cos.size(0) in (1, q.size(0)) and cos.size(1) == q.size(2) and cos.size(2) == q.size(3),
+               "cos, sin must be [batch or 1, seq, dim]")
+        _check(q.dtype == k.dtype == cos.dtype == sin.dtype and q.dtype in _DTYPES,
+               "q, k, cos, sin must share one of fp16 / bf16")
+        _check(q.size(3) % 16 == 0, "rope: hidden dimension must be a multiple of 16")
+        _check(q.is_cuda and k.is_cuda and cos.is_cuda and sin.is_cuda, "q, k, cos, sin must be on CUDA device")
+        if not _tma_compatible(q) or q.stride(3) != 1:
+            q = q.contiguous()
+        if not _tma_compatible(k) or k.stride(3) != 1:
+            k = k.contiguous()
+        if cos.stride(2) != 1 or cos.stride(1) % 8 or cos.data_ptr() % 16 or (cos.size(0) > 1 and cos.stride(0) % 8):
+            cos = cos.contiguous()
+        if sin.stride() != cos.stride() or sin.data_ptr() % 16:
+            cos, sin = cos.contiguous(), sin.contiguous()
+        q_out, k_out = torch.empty_like(q), torch.empty_like(k)
+        if q_out.stride() != q.stride():
+            q_out = torch.empty(q.shape, dtype=q.dtype, device=q.device)
+        if k_out.stride() != k.stride():
+            k_out = torch.empty(k.shape, dtype=k.dtype, device=k.device)
+        p = _lib.RopeParams()
+        p.q, p.k, p.q_out, p.k_out = q.data_ptr(), k.data_ptr(), q_out.data_ptr(), k_out.data_ptr()
+        p.cos, p.sin = cos.data_ptr(), sin.data_ptr()
+        p.batch, p.heads_q, p.seqlen, p.headdim = q.shape
+        p.heads_kv = k.size(1)
+        for dst, t in ((p.q_strides, q), (p.k_strides, k), (p.q_out_strides, q_out), (p.k_out_strides, k_out)):
+            dst[0], dst[1], dst[2] = t.stride(0), t.stride(1), t.stride(2)
+        p.cos_sin_strides[0] = cos.stride(0) if cos.size(0) > 1 else 0
+        p.cos_sin_strides[1] = cos.stride(1)
+        p.dtype = _DTYPES[q.dtype]
+        p.device = q.device.index if q.device.index is not None else torch.cuda.current_device()
+        stream = torch.cuda.current_stream(q.device).cuda_stream
+        _lib.raise_for_status(self._lib.fa_sm100_rope(ctypes.byref(p), ctypes.c_void_p(stream)))
+        return q_out, k_out
+
     def decode_plan(self, q, k, v) -> dict:
         """Split the decode kernel would use for these shapes (no launch; works without a GPU)."""
         params = fill_params(q, k, v, q, 1.0, False, 0)

@@ -27,8 +27,27 @@ def rotate_half(x):
     return torch.cat((-x[..., half:], x[..., :half]), dim=-1)
 
 
+def _fused_rope_applies(q, k, cos, sin, unsqueeze_dim) -> bool:
+    return (q.is_cuda and unsqueeze_dim == 1 and q.dim() == 4 and k.dim() == 4 and cos.dim() == 3
+            and q.dtype in (torch.float16, torch.bfloat16)
+            and q.dtype == k.dtype == cos.dtype == sin.dtype
+            and q.size(-1) % 16 == 0 and cos.size(-1) == q.size(-1) and cos.shape == sin.shape
+            and cos.size(1) == q.size(2) == k.size(2) and cos.size(0) in (1, q.size(0))
+            and not (q.requires_grad or k.requires_grad))
+
+
 def apply_rotary_pos_emb(q, k, cos, sin, position_ids=None, unsqueeze_dim=1):
-    """q_embed = q·cos + rotate_half(q)·sin (same for k); cos/sin are [B, S, D]."""
+    """q_embed = q·cos + rotate_half(q)·sin (same for k); cos/sin are [B, S, D].
+
+    On the GPU, for the layout the model path produces (16-bit, [B,H,S,D] views, cos/sin of the
+    same dtype), this is ONE kernel (`fa_sm100_rope`, csrc/fa_sm100_rope.cuh) that is bit-equal to
+    the expression below; the six elementwise passes and five temporaries of the eager form go
+    away.  Anything else (CPU tensors of the host-logic tests, autograd, exotic
+    broadcasting) evaluates the reference's expression as written."""
+    if _fused_rope_applies(q, k, cos, sin, unsqueeze_dim):
+        from flash_attention_cute_b200.load_cpp_extention import load_extension
+
+        return load_extension().rope(q, k, cos, sin)
     cos = cos.unsqueeze(unsqueeze_dim)
     sin = sin.unsqueeze(unsqueeze_dim)
     return (q * cos) + (rotate_half(q) * sin), (k * cos) + (rotate_half(k) * sin)

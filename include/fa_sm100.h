@@ -113,6 +113,39 @@ int fa_sm100_decode_plan(const fa_sm100_fwd_params* params, int32_t* nsplit, int
 int fa_sm100_fwd_decode(const fa_sm100_fwd_params* params, void* workspace, int64_t workspace_bytes,
                         void* stream);
 
+/* ---- Rotary position embedding on q and k, one pass ----------------------------------------------
+ * Replaces apply_rotary_pos_emb / rotate_half of the reference's model path
+ * (models/rope_attn_fwd.py:8-12, 14-38, call at :87-88):
+ *     out = x * cos + rotate_half(x) * sin,   rotate_half(x) = cat(-x[D/2:], x[:D/2])
+ * for q [B, Hq, S, D] and k [B, Hkv, S, D] (any strides with unit last-dim stride — the
+ * [B, S, H, D]-memory views of the projections run as they are), cos / sin [B or 1, S, D] of the
+ * same dtype.  Rounding follows PyTorch's 16-bit evaluation exactly (each multiply and the add
+ * rounded to the dtype), so the result is bit-equal to the reference expression.  q_out / k_out
+ * may alias q / k (in place).  D must be a multiple of 16. */
+typedef struct fa_sm100_rope_params {
+    const void* q;
+    const void* k;
+    void* q_out;
+    void* k_out;
+    const void* cos;
+    const void* sin;
+    int64_t batch;
+    int64_t heads_q;
+    int64_t heads_kv;
+    int64_t seqlen;
+    int64_t headdim;
+    /* element strides: [0] batch, [1] head, [2] sequence; last-dim stride is 1 */
+    int64_t q_strides[3];
+    int64_t k_strides[3];
+    int64_t q_out_strides[3];
+    int64_t k_out_strides[3];
+    int64_t cos_sin_strides[2]; /* [0] batch (ignored when batch == 1; 0 = broadcast), [1] sequence */
+    int32_t dtype;              /* enum fa_sm100_dtype */
+    int32_t device;
+} fa_sm100_rope_params;
+
+int fa_sm100_rope(const fa_sm100_rope_params* params, void* stream);
+
 /* Thread-local, NUL-terminated description of the last non-zero status on this thread. */
 const char* fa_sm100_last_error(void);
 

@@ -1,0 +1,63 @@
+"""Fused RoPE bandwidth: fa_sm100_rope vs the reference's eager expression, as achieved HBM GB/s
+(algorithmic bytes = q, k read once + q', k' written once; cos/sin are shared by all heads)."""
+import json
+import sys
+from pathlib import Path
+
+import torch
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+from flash_attention_cute_b200.load_cpp_extention import load_extension  # noqa: E402
+from flash_attention_cute_b200.models.rope_attn_fwd import rotate_half  # noqa: E402
+
+SHAPES = {"c3_llama8b_b8_s8k": (8, 32, 8, 8192, 128), "c5_b1_s4k": (1, 32, 8, 4096, 128), "qwen_b4_s2k_d64": (4, 14, 2, 2048, 64)}
+
+
+def timeit(fn, iters=20, warmup=5):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(iters):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / iters
+
+
+def main():
+    dev = torch.device("cuda:0")
+    ext = load_extension()
+    hbm = 6553.0
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        hbm = float(json.loads(p.read_text()).get("hbm_gbs", hbm))
+    out = []
+    for name, (B, Hq, Hkv, S, D) in SHAPES.items():
+        q = torch.randn(B, S, Hq, D, device=dev).bfloat16().transpose(1, 2)
+        k = torch.randn(B, S, Hkv, D, device=dev).bfloat16().transpose(1, 2)
+        ang = torch.rand(1, S, D, device=dev) * 6.28
+        cos, sin = ang.cos().bfloat16(), ang.sin().bfloat16()
+        nbytes = 2 * 2 * B * S * (Hq + Hkv) * D
+
+        def eager():
+            c, s = cos.unsqueeze(1), sin.unsqueeze(1)
+            return (q * c) + (rotate_half(q) * s), (k * c) + (rotate_half(k) * s)
+
+        ms_f = timeit(lambda: ext.rope(q, k, cos, sin))
+        ms_e = timeit(eager)
+        a, b = ext.rope(q, k, cos, sin), eager()
+        rec = {"shape": name, "B": B, "Hq": Hq, "Hkv": Hkv, "S": S, "D": D, "bytes": nbytes,
+               "fused_us": ms_f * 1e3, "fused_gbs": nbytes / ms_f / 1e6, "frac_hbm": nbytes / ms_f / 1e6 / hbm,
+               "eager_us": ms_e * 1e3, "speedup": ms_e / ms_f, "hbm_peak_gbs": hbm,
+               "bit_equal": bool(torch.equal(a[0], b[0]) and torch.equal(a[1], b[1]))}
+        out.append(rec)
+        print(json.dumps(rec), flush=True)
+    if len(sys.argv) > 1:
+        Path(sys.argv[1]).write_text(json.dumps(out, indent=1))
+
+
+if __name__ == "__main__":
+    main()
