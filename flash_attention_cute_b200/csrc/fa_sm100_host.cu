@@ -704,7 +704,8 @@ extern "C" int fa_sm100_rope(const fa_sm100_rope_params* p, void* stream) {
         return fail(FA_SM100_ERR_INVALID_ARGUMENT,
                     "rope: strides must be non-negative multiples of 8 elements (16 bytes)");
     const long long total = (long long)p->batch * p->seqlen * (p->heads_q + p->heads_kv) * (p->headdim / 16);
-    if (p->seqlen > (1ll << 30) || p->heads_q + p->heads_kv > (1 << 20) || total > (1ll << 40))
+    if (p->seqlen > (1ll << 30) || p->heads_q + p->heads_kv > (1 << 20) || total > (1ll << 40) ||
+        p->batch * p->seqlen > 0x7fffffffll)
         return fail(FA_SM100_ERR_INVALID_ARGUMENT, "problem size out of range");
 
     DeviceState* st = device_state(p->device);
@@ -735,7 +736,7 @@ extern "C" int fa_sm100_rope(const fa_sm100_rope_params* p, void* stream) {
     kp.cs_ss = p->cos_sin_strides[1];
     kp.total = total;
     // enough CTAs to keep every SM's load queue full (8 per SM), grid-stride over the rest
-    long long blocks = (total + fa100::rope::kThreads - 1) / fa100::rope::kThreads;
+    long long blocks = (long long)p->batch * p->seqlen;  // one (batch, position) row per loop turn
     const long long cap = 8ll * (st->num_sms > 0 ? st->num_sms : 148);
     if (blocks > cap) blocks = cap;
     if (p->dtype == FA_SM100_BF16)

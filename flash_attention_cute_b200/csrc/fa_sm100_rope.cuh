@@ -36,82 +36,90 @@ struct RopeParams {
     long long total;                           // B * S * (Hq + Hkv) * (D / 16) work items
 };
 
+// out = rn(rn(x * c) + rn(r * s)) on a pair of packed 16-bit values.  The packed hardware ops
+// round the exact product / sum once; PyTorch's "compute in fp32, round to the dtype" gives the
+// same bits (the fp32 product of two 16-bit values is exact, and an fp32 sum that is inexact has
+// an addend too small to reach a rounding midpoint of the larger one).  The _rn forms keep ptxas
+// from fusing multiply and add into one FMA, which would drop a rounding.
 template <bool kBf16>
-struct Cvt;
-template <>
-struct Cvt<true> {
-    static __device__ __forceinline__ float2 up(uint32_t x) {
-        return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&x));
+__device__ __forceinline__ uint32_t rot2(uint32_t x, uint32_t r, uint32_t rsign, uint32_t c, uint32_t s) {
+    r ^= rsign;  // negate both lanes (0x80008000) or neither (0)
+    if constexpr (kBf16) {
+        using V = __nv_bfloat162;
+        const V a = __hmul2_rn(*reinterpret_cast<const V*>(&x), *reinterpret_cast<const V*>(&c));
+        const V b = __hmul2_rn(*reinterpret_cast<const V*>(&r), *reinterpret_cast<const V*>(&s));
+        const V o = __hadd2_rn(a, b);
+        return *reinterpret_cast<const uint32_t*>(&o);
+    } else {
+        using V = __half2;
+        const V a = __hmul2_rn(*reinterpret_cast<const V*>(&x), *reinterpret_cast<const V*>(&c));
+        const V b = __hmul2_rn(*reinterpret_cast<const V*>(&r), *reinterpret_cast<const V*>(&s));
+        const V o = __hadd2_rn(a, b);
+        return *reinterpret_cast<const uint32_t*>(&o);
     }
-    static __device__ __forceinline__ float rn(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
-    static __device__ __forceinline__ uint32_t down(float a, float b) {
-        __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
-        return *reinterpret_cast<uint32_t*>(&t);
-    }
-};
-template <>
-struct Cvt<false> {
-    static __device__ __forceinline__ float2 up(uint32_t x) {
-        return __half22float2(*reinterpret_cast<const __half2*>(&x));
-    }
-    static __device__ __forceinline__ float rn(float x) { return __half2float(__float2half_rn(x)); }
-    static __device__ __forceinline__ uint32_t down(float a, float b) {
-        __half2 t = __floats2half2_rn(a, b);
-        return *reinterpret_cast<uint32_t*>(&t);
-    }
-};
-
-// out = rn(rn(x * c) + rn(r * s)) on a pair of packed 16-bit values
-template <bool kBf16>
-__device__ __forceinline__ uint32_t rot2(uint32_t x, uint32_t r, float rsign, uint32_t c, uint32_t s) {
-    using C = Cvt<kBf16>;
-    const float2 xf = C::up(x), rf = C::up(r), cf = C::up(c), sf = C::up(s);
-    const float a0 = C::rn(xf.x * cf.x), a1 = C::rn(xf.y * cf.y);
-    const float b0 = C::rn(rsign * rf.x * sf.x), b1 = C::rn(rsign * rf.y * sf.y);
-    return C::down(a0 + b0, a1 + b1);
 }
 
+// Four (batch, position) rows — all heads of q and k, contiguous in the [B, S, H, D] memory the
+// projections write — per loop turn of a CTA (their loads are issued together); a thread owns one 16-byte chunk of the first half
+// of a head and its partner in the second half.  32-bit index arithmetic only: at 64 B of traffic
+// per item the budget is ~350 thread instructions per item per SM (HBM 6.5 TB/s), which 64-bit
+// divisions and an fp32 emulation of the three roundings had used up (4.5 TB/s measured).
 template <bool kBf16>
 __global__ void __launch_bounds__(kThreads)
 fa_rope_sm100(const RopeParams p) {
     const int half = p.headdim / 2;
-    const int chunks = p.headdim / 16;  // 16-byte chunks in one half of a head
-    const int htot = p.heads_q + p.heads_kv;
-    const long long stride = static_cast<long long>(gridDim.x) * kThreads;
-    for (long long i = static_cast<long long>(blockIdx.x) * kThreads + threadIdx.x; i < p.total; i += stride) {
-        const int c = static_cast<int>(i % chunks);
-        long long t = i / chunks;
-        const int h = static_cast<int>(t % htot);
-        t /= htot;
-        const int s = static_cast<int>(t % p.seqlen);
-        const int b = static_cast<int>(t / p.seqlen);
-        const bool is_q = h < p.heads_q;
-        const int hh = is_q ? h : h - p.heads_q;
-        const int64_t* ss = is_q ? p.q_s : p.k_s;
-        const int64_t* os = is_q ? p.qo_s : p.ko_s;
-        const uint16_t* src = reinterpret_cast<const uint16_t*>(is_q ? p.q : p.k) + b * ss[0] + hh * ss[1] + s * ss[2] + c * 8;
-        uint16_t* dst = reinterpret_cast<uint16_t*>(is_q ? p.q_out : p.k_out) + b * os[0] + hh * os[1] + s * os[2] + c * 8;
-        const int64_t cs = b * p.cs_sb + s * p.cs_ss + c * 8;
-        const uint16_t* cosp = reinterpret_cast<const uint16_t*>(p.cos) + cs;
-        const uint16_t* sinp = reinterpret_cast<const uint16_t*>(p.sin) + cs;
-        const uint4 x1 = *reinterpret_cast<const uint4*>(src);
-        const uint4 x2 = *reinterpret_cast<const uint4*>(src + half);
-        const uint4 c1 = __ldg(reinterpret_cast<const uint4*>(cosp));
-        const uint4 c2 = __ldg(reinterpret_cast<const uint4*>(cosp + half));
-        const uint4 s1 = __ldg(reinterpret_cast<const uint4*>(sinp));
-        const uint4 s2 = __ldg(reinterpret_cast<const uint4*>(sinp + half));
-        uint4 o1, o2;
-        // first half: x1·cos1 + (−x2)·sin1 ; second half: x2·cos2 + x1·sin2
-        o1.x = rot2<kBf16>(x1.x, x2.x, -1.f, c1.x, s1.x);
-        o1.y = rot2<kBf16>(x1.y, x2.y, -1.f, c1.y, s1.y);
-        o1.z = rot2<kBf16>(x1.z, x2.z, -1.f, c1.z, s1.z);
-        o1.w = rot2<kBf16>(x1.w, x2.w, -1.f, c1.w, s1.w);
-        o2.x = rot2<kBf16>(x2.x, x1.x, 1.f, c2.x, s2.x);
-        o2.y = rot2<kBf16>(x2.y, x1.y, 1.f, c2.y, s2.y);
-        o2.z = rot2<kBf16>(x2.z, x1.z, 1.f, c2.z, s2.z);
-        o2.w = rot2<kBf16>(x2.w, x1.w, 1.f, c2.w, s2.w);
-        *reinterpret_cast<uint4*>(dst) = o1;
-        *reinterpret_cast<uint4*>(dst + half) = o2;
+    const unsigned chunks = p.headdim / 16;  // 16-byte chunks in one half of a head
+    const unsigned items = (p.heads_q + p.heads_kv) * chunks;
+    const unsigned rows = static_cast<unsigned>(p.batch) * p.seqlen;
+    constexpr uint32_t kNeg = 0x80008000u;
+    constexpr int kRowsPerTurn = 4;  // independent rows per loop turn: 8 data loads in flight per thread
+    for (unsigned row0 = blockIdx.x; row0 < rows; row0 += kRowsPerTurn * gridDim.x) {
+        for (unsigned j = threadIdx.x; j < items; j += kThreads) {
+            const unsigned h = j / chunks, c = j - h * chunks;
+            const bool is_q = h < static_cast<unsigned>(p.heads_q);
+            const unsigned hh = is_q ? h : h - p.heads_q;
+            const int64_t* ss = is_q ? p.q_s : p.k_s;
+            const int64_t* os = is_q ? p.qo_s : p.ko_s;
+            const uint16_t* sbase = reinterpret_cast<const uint16_t*>(is_q ? p.q : p.k) + hh * ss[1] + c * 8;
+            uint16_t* dbase = reinterpret_cast<uint16_t*>(is_q ? p.q_out : p.k_out) + hh * os[1] + c * 8;
+            uint4 x1[kRowsPerTurn], x2[kRowsPerTurn], c1[kRowsPerTurn], c2[kRowsPerTurn], s1[kRowsPerTurn], s2[kRowsPerTurn];
+            uint16_t* dst[kRowsPerTurn];
+#pragma unroll
+            for (int u = 0; u < kRowsPerTurn; ++u) {
+                const unsigned row = row0 + u * gridDim.x;
+                dst[u] = nullptr;
+                if (row < rows) {
+                    const unsigned b = row / static_cast<unsigned>(p.seqlen), s = row - b * p.seqlen;
+                    const uint16_t* src = sbase + b * ss[0] + s * ss[2];
+                    dst[u] = dbase + b * os[0] + s * os[2];
+                    const int64_t cs = b * p.cs_sb + s * p.cs_ss + c * 8;
+                    const uint16_t* cosr = reinterpret_cast<const uint16_t*>(p.cos) + cs;
+                    const uint16_t* sinr = reinterpret_cast<const uint16_t*>(p.sin) + cs;
+                    x1[u] = *reinterpret_cast<const uint4*>(src);
+                    x2[u] = *reinterpret_cast<const uint4*>(src + half);
+                    c1[u] = __ldg(reinterpret_cast<const uint4*>(cosr));
+                    c2[u] = __ldg(reinterpret_cast<const uint4*>(cosr + half));
+                    s1[u] = __ldg(reinterpret_cast<const uint4*>(sinr));
+                    s2[u] = __ldg(reinterpret_cast<const uint4*>(sinr + half));
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < kRowsPerTurn; ++u) {
+                if (dst[u] == nullptr) continue;
+                uint4 o1, o2;
+                // first half: x1·cos1 + (−x2)·sin1 ; second half: x2·cos2 + x1·sin2
+                o1.x = rot2<kBf16>(x1[u].x, x2[u].x, kNeg, c1[u].x, s1[u].x);
+                o1.y = rot2<kBf16>(x1[u].y, x2[u].y, kNeg, c1[u].y, s1[u].y);
+                o1.z = rot2<kBf16>(x1[u].z, x2[u].z, kNeg, c1[u].z, s1[u].z);
+                o1.w = rot2<kBf16>(x1[u].w, x2[u].w, kNeg, c1[u].w, s1[u].w);
+                o2.x = rot2<kBf16>(x2[u].x, x1[u].x, 0u, c2[u].x, s2[u].x);
+                o2.y = rot2<kBf16>(x2[u].y, x1[u].y, 0u, c2[u].y, s2[u].y);
+                o2.z = rot2<kBf16>(x2[u].z, x1[u].z, 0u, c2[u].z, s2[u].z);
+                o2.w = rot2<kBf16>(x2[u].w, x1[u].w, 0u, c2[u].w, s2[u].w);
+                *reinterpret_cast<uint4*>(dst[u]) = o1;
+                *reinterpret_cast<uint4*>(dst[u] + half) = o2;
+            }
+        }
     }
 }
 
