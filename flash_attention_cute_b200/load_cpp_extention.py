@@ -36,6 +36,13 @@ def _tma_compatible(t: torch.Tensor) -> bool:
     return True
 
 
+def _compatible_copy(t: torch.Tensor) -> torch.Tensor:
+    """One dense copy with an aligned base (`.contiguous()` alone returns a contiguous tensor as it is,
+    misaligned storage offset included)."""
+    c = t.contiguous()
+    return c.clone() if c.data_ptr() % 16 else c
+
+
 def fill_params(q, k, v, o, softmax_scale: float, causal: bool, flags: int = 0) -> _lib.FwdParams:
     p = _lib.FwdParams()
     p.q, p.k, p.v, p.o = q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr()
@@ -62,9 +69,33 @@ class FlashAttentionExtension:
     def __init__(self) -> None:
         self._lib = _lib.load()
         self._workspaces = {}
+        self._plans = {}  # problem key -> (FwdParams bytes, use_decode, workspace bytes, o strides)
 
     def flash_attention_fwd(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor,
                             softmax_scale: float, causal: bool, flags: int = 0) -> torch.Tensor:
+        # Fast path: this exact problem (shapes, strides, dtypes, devices, scale, flags) has been
+        # validated and planned before — only the four pointers change.  The checks, the params
+        # fill and the plan query below cost 25-35 us of Python per call, more than a decode kernel.
+        key = (q.shape, q.stride(), k.shape, k.stride(), v.shape, v.stride(), q.dtype, k.dtype, v.dtype,
+               q.device, k.device, v.device, float(softmax_scale), bool(causal), int(flags))
+        ent = self._plans.get(key)
+        if ent is not None and not ((q.data_ptr() | k.data_ptr() | v.data_ptr()) & 15):
+            o = torch.empty_like(q)
+            if o.stride() == ent[3] and not (o.data_ptr() & 15):
+                params = _lib.FwdParams.from_buffer_copy(ent[0])
+                params.q, params.k, params.v, params.o = q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr()
+                stream = torch.cuda.current_stream(q.device).cuda_stream
+                if ent[1]:
+                    ws = self._workspace_for(ent[2], q.device, stream)
+                    rc = self._lib.fa_sm100_fwd_decode(ctypes.byref(params),
+                                                       ctypes.c_void_p(ws.data_ptr() if ws is not None else 0),
+                                                       ctypes.c_int64(ws.numel() if ws is not None else 0),
+                                                       ctypes.c_void_p(stream))
+                else:
+                    rc = self._lib.fa_sm100_fwd(ctypes.byref(params), ctypes.c_void_p(stream))
+                _lib.raise_for_status(rc)
+                return o
+
         # --- the reference's checks, csrc/flash_attention_api.cpp:22-59 ---
         _check(q.dim() == 4 and k.dim() == 4 and v.dim() == 4, "q, k, v must be 4-D [batch, heads, seq, dim]")
         _check(q.size(0) == k.size(0) and q.size(0) == v.size(0), "q, k, v must have the same batch size")
@@ -89,23 +120,30 @@ class FlashAttentionExtension:
         _check(q.device == k.device and q.device == v.device, "q, k, v must be on the same CUDA device")
 
         # TMA needs 16-byte aligned bases and strides; anything else gets one contiguous copy.
+        cacheable = True
         if not _tma_compatible(q):
-            q = q.contiguous()
+            q, cacheable = _compatible_copy(q), False
         if not _tma_compatible(k):
-            k = k.contiguous()
+            k, cacheable = _compatible_copy(k), False
         if not _tma_compatible(v):
-            v = v.contiguous()
+            v, cacheable = _compatible_copy(v), False
         o = torch.empty_like(q)  # csrc/flash_attention_api.cpp:85 — O keeps q's strides
         if not _tma_compatible(o) or o.stride(3) != 1:
-            o = torch.empty(q.shape, dtype=q.dtype, device=q.device)
+            o, cacheable = torch.empty(q.shape, dtype=q.dtype, device=q.device), False
 
         params = fill_params(q, k, v, o, softmax_scale, causal, flags)
         stream = torch.cuda.current_stream(q.device).cuda_stream
         # Sq == 1 (the reference's packing branch, csrc/flash_attention_api.cpp:72-83) goes to the
         # split-KV decode kernel whenever it applies: G <= 16 q heads per kv head, positive scale.
-        if (q.size(2) == 1 and q.size(1) // k.size(1) <= DECODE_MAX_GROUP and softmax_scale > 0
-                and not (flags & FLAG_NO_DECODE)):
-            ws = self._decode_workspace(params, q.device, stream)
+        use_decode = (q.size(2) == 1 and q.size(1) // k.size(1) <= DECODE_MAX_GROUP and softmax_scale > 0
+                      and not (flags & FLAG_NO_DECODE))
+        ws_bytes = 0
+        if use_decode:
+            nbytes = ctypes.c_int64()
+            _lib.raise_for_status(self._lib.fa_sm100_decode_plan(ctypes.byref(params), None, None,
+                                                                ctypes.byref(nbytes)))
+            ws_bytes = nbytes.value
+            ws = self._workspace_for(ws_bytes, q.device, stream)
             rc = self._lib.fa_sm100_fwd_decode(ctypes.byref(params),
                                                ctypes.c_void_p(ws.data_ptr() if ws is not None else 0),
                                                ctypes.c_int64(ws.numel() if ws is not None else 0),
@@ -113,6 +151,10 @@ class FlashAttentionExtension:
         else:
             rc = self._lib.fa_sm100_fwd(ctypes.byref(params), ctypes.c_void_p(stream))
         _lib.raise_for_status(rc)
+        if cacheable:
+            if len(self._plans) >= 4096:
+                self._plans.clear()
+            self._plans[key] = (bytes(params), use_decode, ws_bytes, o.stride())
         return o
 
     def rope(self, q: torch.Tensor, k: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor):
@@ -130,9 +172,9 @@ class FlashAttentionExtension:
         _check(q.size(3) % 16 == 0, "rope: hidden dimension must be a multiple of 16")
         _check(q.is_cuda and k.is_cuda and cos.is_cuda and sin.is_cuda, "q, k, cos, sin must be on CUDA device")
         if not _tma_compatible(q) or q.stride(3) != 1:
-            q = q.contiguous()
+            q = _compatible_copy(q)
         if not _tma_compatible(k) or k.stride(3) != 1:
-            k = k.contiguous()
+            k = _compatible_copy(k)
         if cos.stride(2) != 1 or cos.stride(1) % 8 or cos.data_ptr() % 16 or (cos.size(0) > 1 and cos.stride(0) % 8):
             cos = cos.contiguous()
         if sin.stride() != cos.stride() or sin.data_ptr() % 16:
@@ -166,19 +208,16 @@ class FlashAttentionExtension:
         _lib.raise_for_status(rc)
         return {"nsplit": nsplit.value, "chunk": chunk.value, "workspace_bytes": nbytes.value}
 
-    def _decode_workspace(self, params, device, stream):
-        """Grow-only workspace per (device, stream): launches on one stream are ordered, so they can
-        share it; its counter words start zeroed and every launch leaves them zeroed
+    def _workspace_for(self, nbytes: int, device, stream):
+        """Grow-only decode workspace per (device, stream): launches on one stream are ordered, so
+        they can share it; its counter words start zeroed and every launch leaves them zeroed
         (include/fa_sm100.h: fa_sm100_fwd_decode)."""
-        nbytes = ctypes.c_int64()
-        rc = self._lib.fa_sm100_decode_plan(ctypes.byref(params), None, None, ctypes.byref(nbytes))
-        _lib.raise_for_status(rc)
-        if nbytes.value == 0:
+        if nbytes == 0:
             return None
         key = (device.index, stream)
         ws = self._workspaces.get(key)
-        if ws is None or ws.numel() < nbytes.value:
-            ws = torch.zeros(max(nbytes.value, 1 << 22), dtype=torch.uint8, device=device)
+        if ws is None or ws.numel() < nbytes:
+            ws = torch.zeros(max(nbytes, 1 << 22), dtype=torch.uint8, device=device)
             self._workspaces[key] = ws
         return ws
 

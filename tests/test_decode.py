@@ -125,3 +125,23 @@ def test_decode_workspace_is_reusable_and_large_logits(cuda_device):
     for o in outs:
         assert_close(o, ref, torch.float16, "repeat")
     assert all(torch.equal(outs[0], o) for o in outs[1:])
+
+
+@pytest.mark.gpu
+def test_cached_plan_path_matches_first_call(cuda_device):
+    """The operator caches the validated launch plan per problem key; the second call with the same
+    shapes (different data, different buffers) goes through the cache and must agree with the oracle,
+    for the prefill and the decode route alike; a misaligned base pointer falls back to the full path."""
+    ext = _ext()
+    for Sq, Sk in [(1, 900), (200, 200)]:
+        for seed in (1, 2, 3):
+            q, k, v = make_qkv_fast(2, 8, 2, Sq, Sk, 128, torch.float16, seed, cuda_device)
+            out = ext.flash_attention_fwd(q, k, v, 128 ** -0.5, True)
+            assert_close(out, eager_attention(q, k, v, None, True, out_dtype=torch.float32), torch.float16,
+                         f"cached call Sq={Sq} seed={seed}")
+    assert len(ext._plans) >= 2
+    flat = torch.randn(2 * 8 * 200 * 128 + 1, device=cuda_device).half()
+    q_odd = flat[1:].view(2, 8, 200, 128)  # 2-byte offset: not TMA compatible
+    q, k, v = make_qkv_fast(2, 8, 2, 200, 200, 128, torch.float16, 4, cuda_device)
+    out = ext.flash_attention_fwd(q_odd, k, v, 128 ** -0.5, True)
+    assert_close(out, eager_attention(q_odd, k, v, None, True, out_dtype=torch.float32), torch.float16, "misaligned q")
