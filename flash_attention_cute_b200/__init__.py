@@ -3,5 +3,6 @@
 ``flash_attn_func`` is re-exported exactly as the reference's flash_attention/__init__.py:1 does.
 """
 from .flash_attention import flash_attn_func
+from .varlen import flash_attn_varlen_func
 
-__all__ = ["flash_attn_func"]
+__all__ = ["flash_attn_func", "flash_attn_varlen_func"]

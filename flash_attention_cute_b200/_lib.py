@@ -44,6 +44,7 @@ EXPORTED_SYMBOLS = (
     "fa_sm100_fwd",
     "fa_sm100_fwd_decode",
     "fa_sm100_decode_plan",
+    "fa_sm100_fwd_varlen",
     "fa_sm100_rope",
     "fa_sm100_last_error",
     "fa_sm100_check_device",
@@ -72,6 +73,32 @@ class FwdParams(Structure):
         ("k_strides", c_int64 * 3),
         ("v_strides", c_int64 * 3),
         ("o_strides", c_int64 * 3),
+        ("softmax_scale", c_float),
+        ("causal", c_int32),
+        ("dtype", c_int32),
+        ("device", c_int32),
+        ("flags", c_uint32),
+    ]
+
+
+class VarlenParams(Structure):
+    """Mirror of ``struct fa_sm100_varlen_params``."""
+
+    _fields_ = [
+        ("q", c_void_p),
+        ("k", c_void_p),
+        ("v", c_void_p),
+        ("o", c_void_p),
+        ("cu_seqlens_q", POINTER(c_int32)),
+        ("cu_seqlens_kv", POINTER(c_int32)),
+        ("num_seqs", c_int64),
+        ("heads_q", c_int64),
+        ("heads_kv", c_int64),
+        ("headdim", c_int64),
+        ("q_strides", c_int64 * 2),
+        ("k_strides", c_int64 * 2),
+        ("v_strides", c_int64 * 2),
+        ("o_strides", c_int64 * 2),
         ("softmax_scale", c_float),
         ("causal", c_int32),
         ("dtype", c_int32),
@@ -145,6 +172,8 @@ def load() -> ctypes.CDLL:
         lib.fa_sm100_decode_plan.restype = c_int32
         lib.fa_sm100_fwd_decode.argtypes = [POINTER(FwdParams), c_void_p, c_int64, c_void_p]
         lib.fa_sm100_fwd_decode.restype = c_int32
+        lib.fa_sm100_fwd_varlen.argtypes = [POINTER(VarlenParams), c_void_p]
+        lib.fa_sm100_fwd_varlen.restype = c_int32
         lib.fa_sm100_rope.argtypes = [POINTER(RopeParams), c_void_p]
         lib.fa_sm100_rope.restype = c_int32
         lib.fa_sm100_selftest_umma.argtypes = [

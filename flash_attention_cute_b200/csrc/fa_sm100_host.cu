@@ -673,6 +673,73 @@ extern "C" int fa_sm100_fwd_decode(const fa_sm100_fwd_params* p, void* workspace
     return FA_SM100_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Variable-length batches: one forward launch per sequence (include/fa_sm100.h)
+// ---------------------------------------------------------------------------------------------
+extern "C" int fa_sm100_fwd_varlen(const fa_sm100_varlen_params* p, void* stream) {
+    if (!p) return fail(FA_SM100_ERR_INVALID_ARGUMENT, "params is NULL");
+    if (!p->cu_seqlens_q || !p->cu_seqlens_kv)
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT, "cu_seqlens_q / cu_seqlens_kv must be host arrays");
+    if (p->num_seqs < 0) return fail(FA_SM100_ERR_INVALID_ARGUMENT, "num_seqs must be >= 0");
+    if (p->cu_seqlens_q[0] != 0 || p->cu_seqlens_kv[0] != 0)
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT, "cu_seqlens must start at 0");
+    for (int64_t i = 0; i < p->num_seqs; ++i)
+        if (p->cu_seqlens_q[i + 1] < p->cu_seqlens_q[i] || p->cu_seqlens_kv[i + 1] < p->cu_seqlens_kv[i])
+            return fail(FA_SM100_ERR_INVALID_ARGUMENT, "cu_seqlens must be non-decreasing (sequence %lld)",
+                        (long long)i);
+    const int64_t ts[4] = {p->q_strides[0], p->k_strides[0], p->v_strides[0], p->o_strides[0]};
+    for (int j = 0; j < 4; ++j)
+        if (ts[j] % 8 != 0)
+            return fail(FA_SM100_ERR_INVALID_ARGUMENT,
+                        "varlen token strides must be multiples of 8 elements (16 bytes)");
+    for (int64_t i = 0; i < p->num_seqs; ++i) {
+        const int64_t q0 = p->cu_seqlens_q[i], k0 = p->cu_seqlens_kv[i];
+        const int64_t sq = p->cu_seqlens_q[i + 1] - q0, sk = p->cu_seqlens_kv[i + 1] - k0;
+        if (sq == 0) continue;
+        if (sk == 0) {
+            // no visible key: the fixed-length path yields zeros (sum == 0 -> scale 1 on a zero accumulator)
+            cudaError_t e = cudaMemset2DAsync(
+                static_cast<char*>(p->o) + q0 * p->o_strides[0] * 2, size_t(p->o_strides[0]) * 2, 0,
+                size_t(p->heads_q * p->headdim) * 2, size_t(sq), static_cast<cudaStream_t>(stream));
+            if (p->o_strides[1] != p->headdim || e != cudaSuccess)
+                return fail(e != cudaSuccess ? FA_SM100_ERR_CUDA : FA_SM100_ERR_INVALID_ARGUMENT,
+                            "sequence %lld has queries but no keys (needs o head stride == D to zero-fill)",
+                            (long long)i);
+            continue;
+        }
+        fa_sm100_fwd_params f;
+        memset(&f, 0, sizeof(f));
+        f.q = static_cast<const char*>(p->q) + q0 * p->q_strides[0] * 2;
+        f.k = static_cast<const char*>(p->k) + k0 * p->k_strides[0] * 2;
+        f.v = static_cast<const char*>(p->v) + k0 * p->v_strides[0] * 2;
+        f.o = static_cast<char*>(p->o) + q0 * p->o_strides[0] * 2;
+        f.batch = 1;
+        f.heads_q = p->heads_q;
+        f.heads_kv = p->heads_kv;
+        f.seqlen_q = sq;
+        f.seqlen_kv = sk;
+        f.headdim = p->headdim;
+        const int64_t* src[4] = {p->q_strides, p->k_strides, p->v_strides, p->o_strides};
+        int64_t* dst[4] = {f.q_strides, f.k_strides, f.v_strides, f.o_strides};
+        const int64_t rows[4] = {sq, sk, sk, sq};
+        const int64_t heads[4] = {p->heads_q, p->heads_kv, p->heads_kv, p->heads_q};
+        for (int j = 0; j < 4; ++j) {
+            dst[j][2] = src[j][0];
+            dst[j][1] = src[j][1];
+            // batch == 1: any value works; keep it consistent with a dense tensor
+            dst[j][0] = (rows[j] * src[j][0] > heads[j] * src[j][1]) ? rows[j] * src[j][0] : heads[j] * src[j][1];
+        }
+        f.softmax_scale = p->softmax_scale;
+        f.causal = p->causal;
+        f.dtype = p->dtype;
+        f.device = p->device;
+        f.flags = p->flags;
+        int rc = fa_sm100_fwd(&f, stream);
+        if (rc) return rc;
+    }
+    return FA_SM100_OK;
+}
+
 // ------------------------------------------------------------------------------------------------
 // Fused RoPE on q and k: fa_sm100_rope.cuh
 // ------------------------------------------------------------------------------------------------

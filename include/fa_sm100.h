@@ -113,6 +113,43 @@ int fa_sm100_decode_plan(const fa_sm100_fwd_params* params, int32_t* nsplit, int
 int fa_sm100_fwd_decode(const fa_sm100_fwd_params* params, void* workspace, int64_t workspace_bytes,
                         void* stream);
 
+/* ---- Variable-length (packed) batches ---------------------------------------------------------------
+ * SURVEY §8(f) rank 4; the reference lists "varlen" as a TODO (README.md:18) and has no code for it,
+ * so the semantics follow its fixed-length path sequence by sequence: sequence i owns the token rows
+ * cu_seqlens_q[i] .. cu_seqlens_q[i+1] of q / o ([total_q, Hq, D]) and cu_seqlens_kv[i] ..
+ * cu_seqlens_kv[i+1] of k / v ([total_kv, Hkv, D]) and is computed exactly like one batch entry of
+ * fa_sm100_fwd (same GQA rule, same bottom-right causal alignment per sequence).
+ * cu_seqlens_* are HOST arrays of num_seqs + 1 non-decreasing int32 offsets starting at 0 (the
+ * caller already has them on the host to size its buffers; no device read, no sync).  First
+ * implementation: one launch of the forward kernel per non-empty sequence on `stream`, each with its
+ * own tensor maps clipped to the sequence (so no row of a neighbouring sequence is ever read or
+ * written).  Sequences with no queries are skipped; a sequence with queries and no keys writes
+ * zeros.  Token strides must keep every sequence base 16-byte aligned (token stride % 8 == 0). */
+typedef struct fa_sm100_varlen_params {
+    const void* q; /* [total_q,  Hq,  D] */
+    const void* k; /* [total_kv, Hkv, D] */
+    const void* v;
+    void* o;       /* [total_q,  Hq,  D] */
+    const int32_t* cu_seqlens_q;  /* host, num_seqs + 1 entries */
+    const int32_t* cu_seqlens_kv; /* host, num_seqs + 1 entries */
+    int64_t num_seqs;
+    int64_t heads_q;
+    int64_t heads_kv;
+    int64_t headdim;
+    /* element strides: [0] token, [1] head; last-dim stride is 1 */
+    int64_t q_strides[2];
+    int64_t k_strides[2];
+    int64_t v_strides[2];
+    int64_t o_strides[2];
+    float softmax_scale;
+    int32_t causal;
+    int32_t dtype;
+    int32_t device;
+    uint32_t flags;
+} fa_sm100_varlen_params;
+
+int fa_sm100_fwd_varlen(const fa_sm100_varlen_params* params, void* stream);
+
 /* ---- Rotary position embedding on q and k, one pass ----------------------------------------------
  * Replaces apply_rotary_pos_emb / rotate_half of the reference's model path
  * (models/rope_attn_fwd.py:8-12, 14-38, call at :87-88):
