@@ -114,6 +114,8 @@ def test_varlen_parity(case, causal, dtype):
             continue  # rows without a visible key: documented difference (include/fa_sm100.h)
         ref = eager_attention(qi.cpu(), ki.cpu(), vi.cpu(), None, causal)
         assert_close(oi.cpu(), ref.float(), dtype, f"case {case} seq {i}")
+        if sq == 1:
+            continue  # flash_attn_func routes a single query row to the split-KV decode kernel
         same = flash_attn_func(qi, ki, vi, causal=causal)
         assert torch.equal(same, oi), f"case {case} seq {i}: differs from the fixed-length operator"
 
