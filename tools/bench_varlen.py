@@ -43,10 +43,14 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--out", default=None)
+    ap.add_argument("--mixes", default=None, help="comma-separated subset of the mixes")
+    ap.add_argument("--no-comparators", action="store_true")
     args = ap.parse_args()
     hq, hkv, d, dtype = 32, 8, 128, torch.bfloat16
     rows = []
     for name, lens in MIXES.items():
+        if args.mixes and name not in args.mixes.split(","):
+            continue
         g = torch.Generator(device="cuda").manual_seed(7)
         total = sum(lens)
         q = torch.randn(total, hq, d, generator=g, device="cuda").to(dtype)
@@ -61,13 +65,15 @@ def main():
                "varlen_ms": ms, "varlen_tflops": flops / ms / 1e9}
         # the same tokens as a padded fixed-length batch (max length), padding FLOPs not counted
         smax = max(lens)
-        if len(lens) * smax <= 4 * total:
+        if len(lens) * smax <= 4 * total and not args.no_comparators:
             qp = torch.zeros(len(lens), hq, smax, d, device="cuda", dtype=dtype)
             kp = torch.zeros(len(lens), hkv, smax, d, device="cuda", dtype=dtype)
             vp = torch.zeros(len(lens), hkv, smax, d, device="cuda", dtype=dtype)
             ms_p = time_fn(lambda: flash_attn_func(qp, kp, vp, causal=True), args.iters, args.warmup)
             row.update(padded_ms=ms_p, padded_tflops_useful=flops / ms_p / 1e9)
         try:
+            if args.no_comparators:
+                raise RuntimeError("skipped")
             from flash_attn import flash_attn_varlen_func as fa2_varlen
 
             cu_d = torch.tensor(cu, dtype=torch.int32, device="cuda")
