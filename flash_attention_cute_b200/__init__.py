@@ -4,5 +4,6 @@
 """
 from .flash_attention import flash_attn_func
 from .varlen import flash_attn_varlen_func
+from .paged import flash_attn_decode_paged
 
-__all__ = ["flash_attn_func", "flash_attn_varlen_func"]
+__all__ = ["flash_attn_func", "flash_attn_varlen_func", "flash_attn_decode_paged"]

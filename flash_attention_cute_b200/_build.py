@@ -21,8 +21,8 @@ LIB = PKG / "libfa_sm100.so"
 STAMP = PKG / ".libfa_sm100.stamp"
 
 SOURCES = [CSRC / "fa_sm100_host.cu", CSRC / "fa_sm100_selftest.cu"]
-HEADERS = [CSRC / "fa_sm100_kernel.cuh", CSRC / "fa_sm100_fwd.cuh", CSRC / "fa_sm100_fwd4.cuh", CSRC / "fa_sm100_fwd5.cuh", CSRC / "fa_sm100_fwd6.cuh", CSRC / "fa_sm100_decode.cuh", CSRC / "fa_sm100_rope.cuh", CSRC / "fa_sm100_ptx.cuh",
-           ROOT / "include" / "fa_sm100.h"]
+HEADERS = [CSRC / "fa_sm100_fwd.cuh", CSRC / "fa_sm100_sched.cuh", CSRC / "fa_sm100_decode.cuh",
+           CSRC / "fa_sm100_rope.cuh", CSRC / "fa_sm100_ptx.cuh", ROOT / "include" / "fa_sm100.h"]
 
 NVCC_FLAGS = [
     "-O3",
@@ -30,11 +30,15 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo",
     "--expt-relaxed-constexpr",
-    "-DFA_SM100_TUNE",
     "-Xptxas", "-v",
     "-shared",
     "-Xcompiler", "-fPIC",
 ]
+# FA_SM100_TUNE=1 in the environment adds the tuning variants (A/B of exp2 emulation, speculative
+# max, MMA fence; debug timeline) — a development build, never the product (cold build ~25 s
+# without, ~70 s with).
+if os.environ.get("FA_SM100_TUNE", "") not in ("", "0"):
+    NVCC_FLAGS.insert(5, "-DFA_SM100_TUNE")
 
 
 def _nvcc() -> str:
@@ -58,19 +62,34 @@ def is_current() -> bool:
 
 
 def build(force: bool = False, verbose: bool = False) -> Path:
-    """Compile the library if sources changed.  Returns the path of the .so."""
+    """Compile the library if sources changed.  Returns the path of the .so.
+
+    Safe under ``torchrun``: ranks serialise on a file lock, the first one compiles into a
+    temporary file and renames it into place atomically, the others find it current."""
+    import fcntl
+
     if not force and is_current():
         return LIB
-    cmd = [_nvcc(), *NVCC_FLAGS, "-I", str(ROOT / "include"), "-o", str(LIB), *map(str, SOURCES)]
-    proc = subprocess.run(cmd, capture_output=True, text=True)
-    log = proc.stdout + proc.stderr
-    (PKG / "build.log").write_text(" ".join(cmd) + "\n" + log)
-    if proc.returncode != 0:
-        raise RuntimeError(f"nvcc failed building libfa_sm100.so:\n{log[-4000:]}")
-    if verbose:
-        print(log)
-    STAMP.write_text(source_hash())
-    return LIB
+    with open(PKG / ".libfa_sm100.lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and is_current():  # another process built it while we waited
+                return LIB
+            tmp = PKG / f".libfa_sm100.{os.getpid()}.tmp.so"
+            cmd = [_nvcc(), *NVCC_FLAGS, "-I", str(ROOT / "include"), "-o", str(tmp), *map(str, SOURCES)]
+            proc = subprocess.run(cmd, capture_output=True, text=True)
+            log = proc.stdout + proc.stderr
+            (PKG / "build.log").write_text(" ".join(cmd) + "\n" + log)
+            if proc.returncode != 0:
+                tmp.unlink(missing_ok=True)
+                raise RuntimeError(f"nvcc failed building libfa_sm100.so:\n{log[-4000:]}")
+            if verbose:
+                print(log)
+            os.replace(tmp, LIB)
+            STAMP.write_text(source_hash())
+            return LIB
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
 
 
 if __name__ == "__main__":

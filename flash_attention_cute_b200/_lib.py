@@ -16,19 +16,20 @@ FA_SM100_FP16 = 0
 FA_SM100_BF16 = 1
 FLAG_NO_PACK_GQA = 1
 FLAG_FORCE_PACK_GQA = 2
-FLAG_KERNEL_V1 = 4  # debug: first-generation (non-persistent) kernel
+FLAG_NO_DECODE = 8
 
 
-def tune_flags(emu: int | None = None, split: int | None = None, halves: int | None = None) -> int:
-    """Tuning bits of fa_sm100_fwd_params.flags (FA_SM100_TUNE builds): `emu` = exp2 evaluations per
-    4 element pairs moved to the FMA pipe (0-3), `split` = keys of P handed over first (64/96/128)."""
+def tune_flags(emu: int | None = None, spec: bool | None = None, fence: bool | None = None) -> int:
+    """Tuning bits of fa_sm100_fwd_params.flags (honoured by FA_SM100_TUNE=1 builds only): `emu` =
+    exp2 evaluations per 8 element pairs moved to the FMA pipe, `spec` = speculative stale-max
+    softmax, `fence` = tcgen05.fence::after_thread_sync in front of P·V."""
     f = 0
     if emu is not None:
         f |= (int(emu) + 1) << 8
-    if split is not None:
-        f |= {64: 1, 96: 2, 128: 3}[int(split)] << 12
-    if halves is not None:
-        f |= int(halves) << 14
+    if spec is not None:
+        f |= (2 if spec else 1) << 12
+    if fence is not None:
+        f |= (2 if fence else 1) << 14
     return f
 
 STATUS_NAMES = {
@@ -44,13 +45,18 @@ EXPORTED_SYMBOLS = (
     "fa_sm100_fwd",
     "fa_sm100_fwd_decode",
     "fa_sm100_decode_plan",
+    "fa_sm100_paged_decode_plan",
+    "fa_sm100_fwd_decode_paged",
+    "fa_sm100_varlen_workspace_bytes",
     "fa_sm100_fwd_varlen",
     "fa_sm100_rope",
     "fa_sm100_last_error",
     "fa_sm100_check_device",
+    "fa_sm100_set_watchdog_ms",
     "fa_sm100_launch_count",
     "fa_sm100_build_info",
     "fa_sm100_plan",
+    "fa_sm100_kernel_name",
     "fa_sm100_selftest_umma",
 )
 
@@ -89,9 +95,12 @@ class VarlenParams(Structure):
         ("k", c_void_p),
         ("v", c_void_p),
         ("o", c_void_p),
-        ("cu_seqlens_q", POINTER(c_int32)),
-        ("cu_seqlens_kv", POINTER(c_int32)),
+        ("cu_seqlens_q", c_void_p),   # device int32 [num_seqs + 1]
+        ("cu_seqlens_kv", c_void_p),  # device int32 [num_seqs + 1]
         ("num_seqs", c_int64),
+        ("total_q", c_int64),
+        ("total_kv", c_int64),
+        ("max_seqlen_q", c_int64),
         ("heads_q", c_int64),
         ("heads_kv", c_int64),
         ("headdim", c_int64),
@@ -101,6 +110,34 @@ class VarlenParams(Structure):
         ("o_strides", c_int64 * 2),
         ("softmax_scale", c_float),
         ("causal", c_int32),
+        ("dtype", c_int32),
+        ("device", c_int32),
+        ("flags", c_uint32),
+    ]
+
+
+class PagedDecodeParams(Structure):
+    """Mirror of ``struct fa_sm100_paged_decode_params``."""
+
+    _fields_ = [
+        ("q", c_void_p),
+        ("k_cache", c_void_p),
+        ("v_cache", c_void_p),
+        ("o", c_void_p),
+        ("block_table", c_void_p),  # device int32 [B, block_table_stride]
+        ("seqlens_k", c_void_p),    # device int32 [B]
+        ("batch", c_int64),
+        ("heads_q", c_int64),
+        ("heads_kv", c_int64),
+        ("headdim", c_int64),
+        ("page_size", c_int64),
+        ("max_seqlen_k", c_int64),
+        ("block_table_stride", c_int64),
+        ("q_strides", c_int64 * 2),
+        ("o_strides", c_int64 * 2),
+        ("k_strides", c_int64 * 3),
+        ("v_strides", c_int64 * 3),
+        ("softmax_scale", c_float),
         ("dtype", c_int32),
         ("device", c_int32),
         ("flags", c_uint32),
@@ -148,12 +185,20 @@ def load() -> ctypes.CDLL:
         if not _build.is_current():
             try:
                 path = _build.build()
-            except Exception as exc:  # no nvcc on this machine: accept a prebuilt, else fail loudly
-                if not _build.LIB.exists():
+            except Exception as exc:
+                # Never load a library whose sources (kernels, ABI structs) have moved on: that is a
+                # silent mismatch.  FA_SM100_ALLOW_STALE=1 overrides, for machines without nvcc.
+                import os
+                import warnings
+
+                if not _build.LIB.exists() or os.environ.get("FA_SM100_ALLOW_STALE", "") in ("", "0"):
                     raise RuntimeError(
-                        "flash_attention (sm_100a): libfa_sm100.so is missing and could not be built; "
-                        "there is no fallback implementation"
+                        "flash_attention (sm_100a): libfa_sm100.so is missing or older than its sources "
+                        "and could not be rebuilt; there is no fallback implementation "
+                        "(set FA_SM100_ALLOW_STALE=1 to load the stale library anyway)"
                     ) from exc
+                warnings.warn("flash_attention (sm_100a): loading a STALE libfa_sm100.so "
+                              f"(rebuild failed: {exc})", RuntimeWarning)
                 path = _build.LIB
         lib = ctypes.CDLL(str(path))
         lib.fa_sm100_fwd.argtypes = [POINTER(FwdParams), c_void_p]
@@ -172,8 +217,19 @@ def load() -> ctypes.CDLL:
         lib.fa_sm100_decode_plan.restype = c_int32
         lib.fa_sm100_fwd_decode.argtypes = [POINTER(FwdParams), c_void_p, c_int64, c_void_p]
         lib.fa_sm100_fwd_decode.restype = c_int32
-        lib.fa_sm100_fwd_varlen.argtypes = [POINTER(VarlenParams), c_void_p]
+        lib.fa_sm100_paged_decode_plan.argtypes = [POINTER(PagedDecodeParams), POINTER(c_int32), POINTER(c_int32),
+                                                   POINTER(c_int64)]
+        lib.fa_sm100_paged_decode_plan.restype = c_int32
+        lib.fa_sm100_fwd_decode_paged.argtypes = [POINTER(PagedDecodeParams), c_void_p, c_int64, c_void_p]
+        lib.fa_sm100_fwd_decode_paged.restype = c_int32
+        lib.fa_sm100_varlen_workspace_bytes.argtypes = [c_int64]
+        lib.fa_sm100_varlen_workspace_bytes.restype = c_int64
+        lib.fa_sm100_fwd_varlen.argtypes = [POINTER(VarlenParams), c_void_p, c_int64, c_void_p]
         lib.fa_sm100_fwd_varlen.restype = c_int32
+        lib.fa_sm100_set_watchdog_ms.argtypes = [c_int64]
+        lib.fa_sm100_set_watchdog_ms.restype = None
+        lib.fa_sm100_kernel_name.argtypes = [POINTER(FwdParams)]
+        lib.fa_sm100_kernel_name.restype = c_char_p
         lib.fa_sm100_rope.argtypes = [POINTER(RopeParams), c_void_p]
         lib.fa_sm100_rope.restype = c_int32
         lib.fa_sm100_selftest_umma.argtypes = [

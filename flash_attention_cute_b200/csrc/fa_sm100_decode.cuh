@@ -56,7 +56,14 @@ struct DecodeParams {
     int chunk;        // keys per CTA, multiple of kWarps * kTileKeys
     float* part_o;    // [units][nsplit][kRows][kD]  un-normalised O relative to part_ml.m
     float* part_ml;   // [units][nsplit][kRows][2]   (m in the exp2 domain, l)
-    int* counters;    // [units], zero on entry, zero again on exit
+    int* counters;    // [units], zero on entry, zero again on exit (library-owned ring slot)
+    // paged KV (kPaged): k / v are page pools, key j of batch b lives in page
+    // block_table[b * bt_stride + j / page_size] at in-page token j % page_size
+    const int32_t* block_table;
+    const int32_t* seqlens;   // [batch] keys per sequence (seqlen_k is then only the split bound)
+    int64_t bt_stride;
+    int64_t k_sp, v_sp;       // element stride between pages
+    int page_size;            // multiple of kTileKeys
 };
 
 template <int kD>
@@ -127,7 +134,7 @@ __device__ __forceinline__ float fast_exp2(float x) {
     return y;
 }
 
-template <int kD, bool kBf16>
+template <int kD, bool kBf16, bool kPaged>
 __global__ void __launch_bounds__(kThreads, 2)
 fa_decode_sm100(const DecodeParams p) {
     using L = Smem<kD>;
@@ -142,13 +149,22 @@ fa_decode_sm100(const DecodeParams p) {
     const int b = unit / p.heads_kv, kvh = unit - b * p.heads_kv;
     const int G = p.group, D = p.headdim;
     const int key_begin = split * p.chunk;
-    const int key_end = min(p.seqlen_k, key_begin + p.chunk);
+    const int seqlen = kPaged ? p.seqlens[b] : p.seqlen_k;
+    const int key_end = min(seqlen, key_begin + p.chunk);
     const int ntiles = key_end > key_begin ? (key_end - key_begin + kTileKeys - 1) / kTileKeys : 0;
 
     using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
-    const T* kbase = reinterpret_cast<const T*>(p.k) + b * p.k_sb + kvh * p.k_sh;
-    const T* vbase = reinterpret_cast<const T*>(p.v) + b * p.v_sb + kvh * p.v_sh;
+    const T* kbase = reinterpret_cast<const T*>(p.k) + (kPaged ? 0 : b * p.k_sb) + kvh * p.k_sh;
+    const T* vbase = reinterpret_cast<const T*>(p.v) + (kPaged ? 0 : b * p.v_sb) + kvh * p.v_sh;
     const uint32_t ring = smem_addr(smem) + warp * L::kWarpBytes;
+    // Paged: a 16-key tile never straddles a page (page_size % 16 == 0, tiles start at multiples
+    // of 16), so one block-table entry serves the tile; the entry of the NEXT tile this warp will
+    // issue is loaded one issue ahead so that its latency never sits in front of the copies.
+    const int32_t* bt = kPaged ? p.block_table + b * p.bt_stride : nullptr;
+    int phys_pref = 0;
+    if constexpr (kPaged) {
+        if (warp < ntiles) phys_pref = __ldg(bt + (key_begin + warp * kTileKeys) / p.page_size);
+    }
 
     // ---- per-warp cp.async ring ----
     auto issue_tile = [&](int t) {  // t: tile index inside the chunk (this warp's), may be >= ntiles
@@ -156,15 +172,24 @@ fa_decode_sm100(const DecodeParams p) {
             const int stage = (t / kWarps) % kStages;
             const uint32_t dst = ring + stage * L::kStageBytes;
             const int key0 = key_begin + t * kTileKeys;
+            const T* kb = kbase;
+            const T* vb = vbase;
+            int row0 = key0;  // token index of the tile's first row relative to kb / vb
+            if constexpr (kPaged) {
+                const int pg = key0 / p.page_size;
+                row0 = key0 - pg * p.page_size;
+                kb += static_cast<int64_t>(phys_pref) * p.k_sp;
+                vb += static_cast<int64_t>(phys_pref) * p.v_sp;
+                if (t + kWarps < ntiles) phys_pref = __ldg(bt + (key0 + kWarps * kTileKeys) / p.page_size);
+            }
 #pragma unroll
             for (int j = 0; j < kCopies; ++j) {
                 const int i = lane + 32 * j;
                 const int row = i / kChunks, c = i - row * kChunks;
-                const int key = key0 + row;
-                const bool ok = key < key_end && c * 8 < D;
+                const bool ok = key0 + row < key_end && c * 8 < D;
                 const uint32_t off = row * L::kRowBytes + ((c ^ (row & 7)) << 4);
-                cp_async16(dst + off, ok ? kbase + key * p.k_ss + c * 8 : kbase, ok);
-                cp_async16(dst + L::kTileBytes + off, ok ? vbase + key * p.v_ss + c * 8 : vbase, ok);
+                cp_async16(dst + off, ok ? kb + static_cast<int64_t>(row0 + row) * p.k_ss + c * 8 : kbase, ok);
+                cp_async16(dst + L::kTileBytes + off, ok ? vb + static_cast<int64_t>(row0 + row) * p.v_ss + c * 8 : vbase, ok);
             }
         }
         cp_async_commit();  // always commit: the wait below counts groups

@@ -106,34 +106,50 @@ __device__ __forceinline__ bool mbar_try_wait_hint(uint32_t bar, uint32_t parity
 }
 
 // Bounded wait.  A protocol bug in a warp-specialised kernel otherwise hangs the GPU; here every
-// wait gives up after kWatchdogNs, records (code, bar, parity) in the status words and raises the
-// abort flag, after which all waits in the grid fall through so the kernel terminates normally
-// (with garbage output that the host reports as an error, never silently).
-constexpr unsigned long long kWatchdogNs = 4000000000ull;  // 4 s
+// wait gives up after `watchdog_ns` (0 = never), records (code, block, thread) in the status words
+// (device copy + the host-mapped mirror the entry points poll) and raises the abort flag.  A wait
+// that gives up, or that notices the flag while spinning, returns FALSE: the caller's role must
+// leave its loop at once (no further loads of hand-off records, no stores) and fall through to
+// the CTA teardown, so an aborted launch never touches memory it does not own.
+struct WaitCtx {
+    unsigned int* status;        // device: [0] abort flag/code, [1] block, [2] thread, [3] blocked-site mask
+    unsigned int* status_host;   // host-mapped mirror of the same four words (written on abort only)
+    unsigned long long watchdog_ns;
+};
 
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, unsigned int* status,
-                                          uint32_t code) {
-    if (mbar_try_wait(bar, parity)) return;
+// (everything stays inlined: roles that gave registers away with setmaxnreg must not call out)
+__device__ __forceinline__ bool mbar_wait(uint32_t bar, uint32_t parity, const WaitCtx& ctx, uint32_t code) {
+    if (mbar_try_wait(bar, parity)) return true;
     uint64_t t0 = 0;
     uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity)) {
         if ((++spins & 0x3ffu) == 0) {
-            if (*reinterpret_cast<volatile unsigned int*>(status) != 0u) {  // someone aborted
-                atomicOr(status + 3, 1u << (code & 31u));  // leave a trace of every blocked wait site
-                return;
+            if (*reinterpret_cast<volatile unsigned int*>(ctx.status) != 0u) {  // someone aborted
+                atomicOr(ctx.status + 3, 1u << (code & 31u));  // leave a trace of every blocked wait site
+                return false;
             }
+            if (ctx.watchdog_ns == 0ull) continue;
             uint64_t now = global_timer_ns();
             if (t0 == 0) t0 = now;
-            else if (now - t0 > kWatchdogNs) {
-                if (atomicCAS(status, 0u, 0x80000000u | code) == 0u) {
-                    status[1] = blockIdx.x;
-                    status[2] = threadIdx.x;
+            else if (now - t0 > ctx.watchdog_ns) {
+                if (atomicCAS(ctx.status, 0u, 0x80000000u | code) == 0u) {
+                    ctx.status[1] = blockIdx.x;
+                    ctx.status[2] = threadIdx.x;
+                    if (ctx.status_host) {
+                        volatile unsigned int* h = ctx.status_host;
+                        h[1] = blockIdx.x;
+                        h[2] = threadIdx.x;
+                        __threadfence_system();
+                        h[0] = 0x80000000u | code;
+                        __threadfence_system();
+                    }
                 }
-                atomicOr(status + 3, 1u << (code & 31u));
-                return;
+                atomicOr(ctx.status + 3, 1u << (code & 31u));
+                return false;
             }
         }
     }
+    return true;
 }
 
 // ----------------------------------------------------------------------------------------------

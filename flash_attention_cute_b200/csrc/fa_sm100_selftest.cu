@@ -1,5 +1,5 @@
 // UMMA / TMA / TMEM primitive self-test (C ABI: fa_sm100_selftest_umma, include/fa_sm100.h).
-// One CTA runs the exact descriptor recipes of fa_sm100_kernel.cuh in isolation:
+// One CTA runs the exact descriptor recipes of fa_sm100_fwd.cuh in isolation:
 //   S = Q·Kᵀ      SS-mode tcgen05.mma, K-major 128B-swizzled Q and K panels written by TMA
 //   P = T(S * p_scale) packed two-per-column into TMEM by tcgen05.st
 //   O = P·V       TS-mode tcgen05.mma, A from TMEM, V MN-major 128B-swizzled panels
@@ -10,7 +10,7 @@
 #include "../../include/fa_sm100.h"
 #include "fa_sm100_ptx.cuh"
 
-extern "C" unsigned int* fa_sm100_internal_status(int device);
+extern "C" int fa_sm100_internal_wait_ctx(int device, fa100::WaitCtx* out);
 extern "C" int fa_sm100_internal_encode_2d(CUtensorMap* map, int is_bf16, const void* base,
                                            uint64_t rows, uint64_t cols);
 extern "C" void fa_sm100_internal_count_launch(void);
@@ -25,7 +25,7 @@ struct SelftestParams {
     float p_scale;
     uint32_t v_lbo, v_sbo;
     int32_t headdim;
-    unsigned int* status;
+    WaitCtx wait;
 };
 
 template <int kD, bool kBf16>
@@ -69,7 +69,7 @@ __global__ void __launch_bounds__(128, 1) selftest_kernel(const __grid_constant_
                 "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                 ::"r"(sv + pn * kPanelBytes), "l"(reinterpret_cast<uint64_t>(&p.tm_v)), "r"(bars), "r"(pn * 64), "r"(0) : "memory");
         }
-        mbar_wait(bars, 0, p.status, 101);
+        (void)mbar_wait(bars, 0, p.wait, 101);  // a timeout is reported through the status word
         tc_fence_after_sync();
         constexpr uint32_t idesc_qk = make_idesc_f16(kBf16, 128, 128, false, false);
 #pragma unroll
@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(128, 1) selftest_kernel(const __grid_constant_
     // every thread owns one row
     const int r = threadIdx.x;
     const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
-    mbar_wait(bars + 8, 0, p.status, 102);
+    (void)mbar_wait(bars + 8, 0, p.wait, 102);
     tc_fence_after_sync();
     uint32_t pk[64];
 #pragma unroll
@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(128, 1) selftest_kernel(const __grid_constant_
                     idesc_pv, ks > 0);
         tc_commit(bars + 16);
     }
-    mbar_wait(bars + 16, 0, p.status, 103);
+    (void)mbar_wait(bars + 16, 0, p.wait, 103);
     tc_fence_after_sync();
 #pragma unroll
     for (int c = 0; c < kD / 32; ++c) {
@@ -142,10 +142,10 @@ extern "C" int fa_sm100_selftest_umma(const void* q, const void* k, const void* 
                                       uint32_t v_lbo, uint32_t v_sbo, int32_t device, void* stream) {
     if (headdim <= 0 || headdim > 128 || headdim % 8)
         return fa_sm100_internal_fail(FA_SM100_ERR_INVALID_ARGUMENT, "selftest: bad headdim");
-    unsigned int* status = fa_sm100_internal_status(device);
-    if (!status) return fa_sm100_internal_fail(FA_SM100_ERR_CUDA, "selftest: device init failed");
-    cudaSetDevice(device);
     fa100::SelftestParams sp;
+    int rc0 = fa_sm100_internal_wait_ctx(device, &sp.wait);
+    if (rc0) return rc0;
+    cudaSetDevice(device);
     const int bf16 = dtype == FA_SM100_BF16;
     int rc;
     if ((rc = fa_sm100_internal_encode_2d(&sp.tm_q, bf16, q, 128, headdim))) return rc;
@@ -157,7 +157,6 @@ extern "C" int fa_sm100_selftest_umma(const void* q, const void* k, const void* 
     sp.v_lbo = v_lbo;
     sp.v_sbo = v_sbo;
     sp.headdim = headdim;
-    sp.status = status;
     const int kd = headdim <= 64 ? 64 : 128;
     const int smem = 3 * (kd / 64) * 128 * 128 + 128 + 1024;
     using Fn = void (*)(const fa100::SelftestParams);

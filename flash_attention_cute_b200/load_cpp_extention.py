@@ -210,14 +210,15 @@ class FlashAttentionExtension:
 
     def _workspace_for(self, nbytes: int, device, stream):
         """Grow-only decode workspace per (device, stream): launches on one stream are ordered, so
-        they can share it; its counter words start zeroed and every launch leaves them zeroed
-        (include/fa_sm100.h: fa_sm100_fwd_decode)."""
+        they can share it.  It only holds the partial results of one launch — no state survives a
+        launch, whatever the shapes of consecutive calls (include/fa_sm100.h: fa_sm100_fwd_decode;
+        the arrival counters live in a library-owned ring)."""
         if nbytes == 0:
             return None
         key = (device.index, stream)
         ws = self._workspaces.get(key)
         if ws is None or ws.numel() < nbytes:
-            ws = torch.zeros(max(nbytes, 1 << 22), dtype=torch.uint8, device=device)
+            ws = torch.empty(max(nbytes, 1 << 22), dtype=torch.uint8, device=device)
             self._workspaces[key] = ws
         return ws
 

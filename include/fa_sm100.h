@@ -56,16 +56,15 @@ enum fa_sm100_status {
 /* Flags for fa_sm100_fwd_params.flags */
 #define FA_SM100_FLAG_NO_PACK_GQA 1u   /* do not pack the q heads of a kv group into one M tile */
 #define FA_SM100_FLAG_FORCE_PACK_GQA 2u /* pack whenever Hq/Hkv > 1 (default: heuristic)        */
-#define FA_SM100_FLAG_KERNEL_V1 4u      /* debug: first-generation (non-persistent) kernel       */
 #define FA_SM100_FLAG_NO_DECODE 8u      /* operator-level routing hint: keep seqlen_q == 1 on
                                            fa_sm100_fwd instead of fa_sm100_fwd_decode            */
-/* Tuning bits (honoured by FA_SM100_TUNE builds, ignored otherwise):
- *   bits 8-11  1 + number of exp2 evaluations per 4 element pairs moved to the FMA pipe (0 = default)
- *   bits 12-13 P hand-off split: 0 = default, 1 = 64 keys first, 2 = 96, 3 = no split
- *   bits 14-15 softmax threads per query row: 0 = default, 1 or 2                                 */
+/* Tuning bits (honoured by builds with -DFA_SM100_TUNE, ignored by the product build):
+ *   bits 8-11  1 + number of exp2 evaluations per 8 element pairs moved to the FMA pipe (0 = default)
+ *   bits 12-13 speculative stale-max softmax: 0 = default, 1 = off, 2 = on
+ *   bits 14-15 tcgen05.fence::after_thread_sync in front of P·V: 0 = default, 1 = off, 2 = on     */
 #define FA_SM100_FLAG_TUNE_EMU(n) ((uint32_t)((n) + 1) << 8)
-#define FA_SM100_FLAG_TUNE_SPLIT(sel) ((uint32_t)(sel) << 12)
-#define FA_SM100_FLAG_TUNE_HALVES(n) ((uint32_t)(n) << 14)
+#define FA_SM100_FLAG_TUNE_SPEC(sel) ((uint32_t)(sel) << 12)
+#define FA_SM100_FLAG_TUNE_FENCE(sel) ((uint32_t)(sel) << 14)
 
 typedef struct fa_sm100_fwd_params {
     const void* q;      /* device pointers, 16-byte aligned */
@@ -105,34 +104,83 @@ int fa_sm100_fwd(const fa_sm100_fwd_params* params, void* stream);
  * last CTA of a unit merges the partial (max, sum, O) triples, so it is still ONE launch.
  *
  * fa_sm100_decode_plan reports the split the library would use and the workspace it needs
- * (0 bytes when nsplit == 1).  The caller owns the workspace: 256-byte aligned device memory whose
- * first ceil(4·B·Hkv / 256)·256 bytes are ZERO before the first launch that uses it; every launch
- * leaves them zero again, so one buffer serves all stream-ordered launches. */
+ * (0 bytes when nsplit == 1).  The caller owns the workspace: 256-byte aligned device memory that
+ * holds the partial results of the launch only — no state survives a launch and nothing has to be
+ * zeroed, so one buffer (of the largest size any call needs) serves all stream-ordered launches
+ * of any shape.  The per-unit arrival counters live in a library-owned ring. */
 int fa_sm100_decode_plan(const fa_sm100_fwd_params* params, int32_t* nsplit, int32_t* chunk_keys,
                          int64_t* workspace_bytes);
 int fa_sm100_fwd_decode(const fa_sm100_fwd_params* params, void* workspace, int64_t workspace_bytes,
                         void* stream);
+
+/* ---- Paged-KV decode (seqlen_q == 1) -----------------------------------------------------------------
+ * SURVEY §8(f) rank 4; "paged KV cache" is a TODO of the reference (README.md:21), so the contract
+ * is the contiguous decode above applied to the keys a block table names: sequence b owns
+ * seqlens_k[b] keys, key j of it lives in physical page block_table[b * block_table_stride +
+ * j / page_size] at in-page position j % page_size.  k_cache / v_cache element address of
+ * (page, kv-head, in-page token, d) = page * kv_strides[0] + head * kv_strides[1] +
+ * token * kv_strides[2] + d, which covers both [pages, page_size, Hkv, D] and
+ * [pages, Hkv, page_size, D].  page_size must be a multiple of 16.  seqlens_k and block_table are
+ * DEVICE int32 arrays (read by the kernel, no host sync); max_seqlen_k only sizes the split and
+ * must be >= every seqlens_k[b].  Same split-KV kernel, workspace rules and numerics as
+ * fa_sm100_fwd_decode; a sequence with no keys yields zeros. */
+typedef struct fa_sm100_paged_decode_params {
+    const void* q;        /* [B, Hq, D] element strides q_strides = {batch, head} */
+    const void* k_cache;
+    const void* v_cache;
+    void* o;              /* [B, Hq, D] element strides o_strides = {batch, head} */
+    const int32_t* block_table; /* device [B, block_table_stride] */
+    const int32_t* seqlens_k;   /* device [B] */
+    int64_t batch;
+    int64_t heads_q;
+    int64_t heads_kv;
+    int64_t headdim;
+    int64_t page_size;
+    int64_t max_seqlen_k;
+    int64_t block_table_stride;
+    int64_t q_strides[2];
+    int64_t o_strides[2];
+    int64_t k_strides[3]; /* page, head, in-page token */
+    int64_t v_strides[3];
+    float softmax_scale;
+    int32_t dtype;
+    int32_t device;
+    uint32_t flags;
+} fa_sm100_paged_decode_params;
+
+int fa_sm100_paged_decode_plan(const fa_sm100_paged_decode_params* params, int32_t* nsplit,
+                               int32_t* chunk_keys, int64_t* workspace_bytes);
+int fa_sm100_fwd_decode_paged(const fa_sm100_paged_decode_params* params, void* workspace,
+                              int64_t workspace_bytes, void* stream);
 
 /* ---- Variable-length (packed) batches ---------------------------------------------------------------
  * SURVEY §8(f) rank 4; the reference lists "varlen" as a TODO (README.md:18) and has no code for it,
  * so the semantics follow its fixed-length path sequence by sequence: sequence i owns the token rows
  * cu_seqlens_q[i] .. cu_seqlens_q[i+1] of q / o ([total_q, Hq, D]) and cu_seqlens_kv[i] ..
  * cu_seqlens_kv[i+1] of k / v ([total_kv, Hkv, D]) and is computed exactly like one batch entry of
- * fa_sm100_fwd (same GQA rule, same bottom-right causal alignment per sequence).
- * cu_seqlens_* are HOST arrays of num_seqs + 1 non-decreasing int32 offsets starting at 0 (the
- * caller already has them on the host to size its buffers; no device read, no sync).  First
- * implementation: one launch of the forward kernel per non-empty sequence on `stream`, each with its
- * own tensor maps clipped to the sequence (so no row of a neighbouring sequence is ever read or
- * written).  Sequences with no queries are skipped; a sequence with queries and no keys writes
- * zeros.  Token strides must keep every sequence base 16-byte aligned (token stride % 8 == 0). */
+ * fa_sm100_fwd (same GQA rule, same bottom-right causal alignment per sequence; bit-equal results).
+ * cu_seqlens_* are DEVICE arrays of num_seqs + 1 non-decreasing int32 offsets starting at 0 and
+ * ending at total_q / total_kv: nothing is read on the host, nothing synchronises, the call is
+ * CUDA-graph capturable.  ONE persistent launch serves the whole batch (plus a one-CTA plan kernel
+ * in front of it that orders the sequences longest first): the tile scheduler walks the offsets,
+ * the tensor maps span the packed token axis, O rows are clipped per sequence, and V rows that
+ * belong to a neighbouring sequence are zeroed in shared memory before they reach the tensor
+ * core, so no value of another sequence can leak into a result.  Sequences with no queries are
+ * skipped; a sequence with queries and no keys writes zeros.  Token strides must be multiples of
+ * 8 elements.  max_seqlen_q is a hint (0 = unknown) that only steers the GQA packing choice.
+ * The caller owns `workspace`: fa_sm100_varlen_workspace_bytes(num_seqs) bytes of device memory,
+ * 16-byte aligned, contents irrelevant. */
 typedef struct fa_sm100_varlen_params {
     const void* q; /* [total_q,  Hq,  D] */
     const void* k; /* [total_kv, Hkv, D] */
     const void* v;
     void* o;       /* [total_q,  Hq,  D] */
-    const int32_t* cu_seqlens_q;  /* host, num_seqs + 1 entries */
-    const int32_t* cu_seqlens_kv; /* host, num_seqs + 1 entries */
+    const int32_t* cu_seqlens_q;  /* device, num_seqs + 1 entries */
+    const int32_t* cu_seqlens_kv; /* device, num_seqs + 1 entries */
     int64_t num_seqs;
+    int64_t total_q;
+    int64_t total_kv;
+    int64_t max_seqlen_q;
     int64_t heads_q;
     int64_t heads_kv;
     int64_t headdim;
@@ -148,7 +196,9 @@ typedef struct fa_sm100_varlen_params {
     uint32_t flags;
 } fa_sm100_varlen_params;
 
-int fa_sm100_fwd_varlen(const fa_sm100_varlen_params* params, void* stream);
+int64_t fa_sm100_varlen_workspace_bytes(int64_t num_seqs);
+int fa_sm100_fwd_varlen(const fa_sm100_varlen_params* params, void* workspace, int64_t workspace_bytes,
+                        void* stream);
 
 /* ---- Rotary position embedding on q and k, one pass ----------------------------------------------
  * Replaces apply_rotary_pos_emb / rotate_half of the reference's model path
@@ -187,8 +237,16 @@ int fa_sm100_rope(const fa_sm100_rope_params* params, void* stream);
 const char* fa_sm100_last_error(void);
 
 /* Synchronises `device` and reports whether any kernel launched by this library since the last
- * call hit its in-kernel watchdog (test / debug aid; not used on the hot path). */
+ * call hit its in-kernel watchdog; clears the condition.  While the condition is set every entry
+ * point above returns FA_SM100_ERR_KERNEL_ABORT without launching (the flag is mirrored into
+ * host-mapped memory, so that check costs one host load), and launches already queued behind the
+ * aborted one exit at once without touching their outputs. */
 int fa_sm100_check_device(int device);
+
+/* In-kernel watchdog: a wait inside a kernel gives up after `milliseconds` (default 2000; the
+ * environment variable FA_SM100_WATCHDOG_MS sets the initial value; 0 disables the watchdog, e.g.
+ * under a debugger or time-sliced MPS).  Process-wide, takes effect for later launches. */
+void fa_sm100_set_watchdog_ms(int64_t milliseconds);
 
 /* Library / kernel introspection used by tests and bench: number of kernel launches issued by
  * this library in this process, and a static description of the build. */
@@ -199,6 +257,8 @@ const char* fa_sm100_build_info(void);
  * dynamic shared memory bytes, pack factor (1 = unpacked) and q rows per head per tile. */
 int fa_sm100_plan(const fa_sm100_fwd_params* params, int32_t* grid, int32_t* smem_bytes,
                   int32_t* pack_g, int32_t* rows_per_head);
+/* Name of the kernel variant fa_sm100_fwd launches for `params` ("" if they are invalid). */
+const char* fa_sm100_kernel_name(const fa_sm100_fwd_params* params);
 
 /* UMMA/TMA primitive self-test (tests/test_primitives.py): one CTA computes S = Q·Kᵀ
  * (128 x 128, fp32) and O = round(S * p_scale)·V (128 x D, fp32) with the same descriptors the

@@ -29,10 +29,9 @@ def make_qkv_fast(B, Hq, Hkv, Sq, Sk, D, dtype, seed, device):
 
 
 def errors(out, ref):
-    """max-abs error (measured in units of max(1, |ref|): a 16-bit output cannot be closer than
-    half an ulp, 2^-9·|o| for bf16, so for |o| > 1 the absolute bound scales with the magnitude —
-    this only matters for the first causal rows, whose output is a copy of a V row) and the
-    relative L2 error."""
+    """(scaled max-abs, relative L2).  The scaled max-abs divides by max(1, |ref|): identical to the
+    plain absolute error wherever |ref| <= 1, and for larger outputs it grows with the magnitude
+    the way the output format's own rounding does (see assert_close)."""
     out = out.float()
     ref = ref.float()
     diff = out - ref
@@ -41,10 +40,33 @@ def errors(out, ref):
     return max_abs, rel_l2
 
 
+def abs_errors(out, ref):
+    """(plain max-abs over everything, plain max-abs over elements with |ref| <= 1, max |ref|)."""
+    out = out.float()
+    ref = ref.float()
+    diff = (out - ref).abs()
+    small = ref.abs() <= 1.0
+    inner = diff[small].max().item() if small.any() else 0.0
+    return diff.max().item(), inner, ref.abs().max().item()
+
+
+LAST = {}  # the numbers of the most recent assert_close (tests print / tools log them)
+
+
 def assert_close(out, ref32, dtype, what=""):
+    """BASELINE.json north_star: max-abs <= 2e-3 (fp16) / 1e-2 (bf16), relative-L2 <= 1e-3 / 5e-3.
+    The absolute bound is asserted AS STATED on every element with |ref| <= 1.  Above that a
+    16-bit output cannot meet it even when correctly rounded (half an ulp of bf16 is 1.6e-2 at
+    |o| = 4 — the first causal rows copy V rows of that size), so those elements are held to the
+    same bound relative to |ref|; the plain absolute maximum and the largest |ref| are recorded
+    in LAST and shown on failure."""
     assert torch.isfinite(out.float()).all(), f"{what}: non-finite values in output"
     max_abs, rel_l2 = errors(out, ref32)
+    plain, inner, ref_max = abs_errors(out, ref32)
     tol = TOL[dtype]
-    assert max_abs <= tol["max_abs"] and rel_l2 <= tol["rel_l2"], (
-        f"{what}: max_abs={max_abs:.3e} (tol {tol['max_abs']:.0e}), rel_l2={rel_l2:.3e} (tol {tol['rel_l2']:.0e})")
+    LAST.update(what=what, max_abs_scaled=max_abs, max_abs_plain=plain, max_abs_ref_le_1=inner,
+                ref_abs_max=ref_max, rel_l2=rel_l2)
+    assert inner <= tol["max_abs"] and max_abs <= tol["max_abs"] and rel_l2 <= tol["rel_l2"], (
+        f"{what}: max_abs(|ref|<=1)={inner:.3e}, scaled max_abs={max_abs:.3e} (tol {tol['max_abs']:.0e}), "
+        f"plain max_abs={plain:.3e} at max|ref|={ref_max:.2f}, rel_l2={rel_l2:.3e} (tol {tol['rel_l2']:.0e})")
     return max_abs, rel_l2

@@ -28,7 +28,7 @@ def test_plan_reference_decode_case():
     # scripts/benchmark_kernel.py usage example: B=16, 64/8 heads, Sk=1024 -> 128 units, 2 splits
     p = _plan(16, 64, 8, 1024)
     assert p["nsplit"] == 2 and p["chunk"] == 512
-    assert p["workspace_bytes"] >= 128 * 2 * 16 * (128 + 2) * 4
+    assert p["workspace_bytes"] == 128 * 2 * 16 * (128 + 2) * 4  # partials only: no counter region
 
 
 def test_plan_one_wave_and_chunk_granularity():
@@ -145,3 +145,120 @@ def test_cached_plan_path_matches_first_call(cuda_device):
     q, k, v = make_qkv_fast(2, 8, 2, 200, 200, 128, torch.float16, 4, cuda_device)
     out = ext.flash_attention_fwd(q_odd, k, v, 128 ** -0.5, True)
     assert_close(out, eager_attention(q_odd, k, v, None, True, out_dtype=torch.float32), torch.float16, "misaligned q")
+
+
+@pytest.mark.gpu
+def test_decode_shape_changes_on_one_stream(cuda_device):
+    """one grow-only workspace per stream serves every shape.  A call with few
+    units and many splits followed by one with more units must not find its arrival counters
+    clobbered by the first call's partials (the counters now live in a library-owned ring, the
+    workspace holds partial results only)."""
+    shapes = [(1, 32, 8, 6000), (16, 64, 8, 1024), (2, 32, 8, 3000), (16, 64, 8, 1024), (1, 8, 8, 9000),
+              (9, 64, 8, 2048), (16, 64, 8, 1024)]
+    for i, (B, Hq, Hkv, Sk) in enumerate(shapes):
+        q, k, v = make_qkv_fast(B, Hq, Hkv, 1, Sk, 128, torch.bfloat16, 50 + i, cuda_device)
+        plan = _ext().decode_plan(q, k, k)
+        assert plan["nsplit"] > 1
+        out = _run(q, k, v)
+        assert_close(out, eager_attention(q, k, v, None, False, out_dtype=torch.float32), torch.bfloat16,
+                     f"call {i}: B={B} units={B * Hkv} nsplit={plan['nsplit']}")
+
+
+# ------------------------------------------------------------------ paged KV cache
+def _paged_case(B, Hq, Hkv, D, page, lens, dtype, device, seed, layout="pshd", shared=False):
+    """Random pages in random order; returns (q, k_cache, v_cache, block_table, seqlens, dense k, dense v)."""
+    g = torch.Generator(device=device).manual_seed(seed)
+    max_pages = (max(lens) + page - 1) // page
+    n_pages = B * max_pages + 3
+    if layout == "pshd":
+        kc = torch.randn(n_pages, page, Hkv, D, generator=g, device=device).to(dtype)
+        vc = torch.randn(n_pages, page, Hkv, D, generator=g, device=device).to(dtype)
+    else:  # storage [pages, Hkv, page, D], handed over as a [pages, page, Hkv, D] view
+        kc = torch.randn(n_pages, Hkv, page, D, generator=g, device=device).to(dtype).transpose(1, 2)
+        vc = torch.randn(n_pages, Hkv, page, D, generator=g, device=device).to(dtype).transpose(1, 2)
+    perm = torch.randperm(n_pages, generator=g, device=device).to(torch.int32)
+    bt = perm[: B * max_pages].view(B, max_pages).contiguous()
+    if shared:  # every sequence starts with the same (prefix) page
+        bt[:, 0] = bt[0, 0]
+    q = torch.randn(B, Hq, D, generator=g, device=device).to(dtype)
+    sl = torch.tensor(lens, dtype=torch.int32, device=device)
+    dense_k = kc[bt.long()].reshape(B, max_pages * page, Hkv, D).transpose(1, 2)  # [B, Hkv, S, D]
+    dense_v = vc[bt.long()].reshape(B, max_pages * page, Hkv, D).transpose(1, 2)
+    return q, kc, vc, bt, sl, dense_k, dense_v
+
+
+def test_paged_plan_validation():
+    import ctypes
+
+    from flash_attention_cute_b200 import _lib
+
+    lib = _lib.load()
+    p = _lib.PagedDecodeParams()
+    p.q = p.k_cache = p.v_cache = p.o = p.block_table = p.seqlens_k = 256
+    p.batch, p.heads_q, p.heads_kv, p.headdim = 16, 64, 8, 128
+    p.page_size, p.max_seqlen_k, p.block_table_stride = 128, 8192, 64
+    p.q_strides[0], p.q_strides[1] = 64 * 128, 128
+    p.o_strides[0], p.o_strides[1] = 64 * 128, 128
+    for st in (p.k_strides, p.v_strides):
+        st[0], st[1], st[2] = 128 * 8 * 128, 128, 8 * 128
+    p.softmax_scale = 0.088
+    ns, ch, nb = ctypes.c_int32(), ctypes.c_int32(), ctypes.c_int64()
+    assert lib.fa_sm100_paged_decode_plan(ctypes.byref(p), ctypes.byref(ns), ctypes.byref(ch), ctypes.byref(nb)) == 0
+    assert ns.value == 2 and ch.value == 4096 and nb.value == 128 * 2 * 16 * (128 + 2) * 4
+    p.page_size = 24
+    assert lib.fa_sm100_paged_decode_plan(ctypes.byref(p), None, None, None) == 1
+    assert "multiple of 16" in _lib.last_error()
+    p.page_size, p.block_table_stride = 128, 8
+    assert lib.fa_sm100_paged_decode_plan(ctypes.byref(p), None, None, None) == 1
+    assert "smaller than max_seqlen_k" in _lib.last_error()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16], ids=["fp16", "bf16"])
+@pytest.mark.parametrize("B,Hq,Hkv,D,page,lens,layout,shared", [
+    (4, 32, 8, 128, 128, [1000, 517, 128, 1], "pshd", False),      # ragged last pages, a single key
+    (2, 14, 2, 64, 16, [333, 40], "pshd", False),                   # smallest page, D = 64
+    (3, 16, 1, 128, 256, [4096, 0, 2500], "pshd", False),           # an empty sequence -> zeros
+    (16, 64, 8, 128, 128, [8192] * 16, "phsd", False),              # the measured shape, head-major pages
+    (5, 8, 8, 128, 64, [700, 64, 65, 63, 1024], "pshd", True),      # shared prefix page
+    (1, 32, 8, 128, 128, [32768], "pshd", False),                   # one long sequence, many splits
+])
+def test_paged_decode_matches_oracle(cuda_device, dtype, B, Hq, Hkv, D, page, lens, layout, shared):
+    from flash_attention import flash_attn_decode_paged
+    from flash_attention_cute_b200 import _lib
+
+    q, kc, vc, bt, sl, dk, dv = _paged_case(B, Hq, Hkv, D, page, lens, dtype, cuda_device, 77, layout, shared)
+    n0 = _lib.launch_count()
+    out = flash_attn_decode_paged(q, kc, vc, bt, sl, max_seqlen_k=max(max(lens), 1))
+    _lib.check_device(0)
+    assert _lib.launch_count() == n0 + 1 and out.shape == q.shape
+    for b, n in enumerate(lens):
+        if n == 0:
+            assert not out[b].any()
+            continue
+        ref = eager_attention(q[b:b + 1].unsqueeze(2), dk[b:b + 1, :, :n], dv[b:b + 1, :, :n], None, False,
+                              out_dtype=torch.float32)
+        assert_close(out[b:b + 1].unsqueeze(2), ref, dtype, f"paged seq {b} len {n}")
+    # same keys through the contiguous decode kernel: bit-equal when the split is the same
+    if len(set(lens)) == 1 and lens[0] % page == 0:
+        dense = _ext().flash_attention_fwd(q.unsqueeze(2), dk.contiguous(), dv.contiguous(), D ** -0.5, False)
+        assert torch.equal(dense[:, :, 0], out)
+
+
+@pytest.mark.gpu
+def test_paged_decode_ignores_pages_past_the_sequence(cuda_device):
+    from flash_attention import flash_attn_decode_paged
+
+    q, kc, vc, bt, sl, dk, dv = _paged_case(3, 32, 8, 128, 128, [300, 1024, 129], torch.bfloat16, cuda_device, 5)
+    ref = flash_attn_decode_paged(q, kc, vc, bt, sl)
+    used = torch.zeros(kc.size(0), dtype=torch.bool, device=cuda_device)
+    for b, n in enumerate([300, 1024, 129]):
+        used[bt[b, : (n + 127) // 128].long()] = True
+    kc2, vc2 = kc.clone(), vc.clone()
+    kc2[~used] = float("nan")
+    vc2[~used] = float("nan")
+    bt2 = bt.clone()
+    for b, n in enumerate([300, 1024, 129]):   # table entries past the sequence may hold anything valid
+        bt2[b, (n + 127) // 128:] = 0
+    out = flash_attn_decode_paged(q, kc2, vc2, bt2, sl)
+    assert torch.equal(out, ref)

@@ -1,9 +1,10 @@
-"""Interleaved A/B timing of tuning variants (FA_SM100_TUNE builds): every configuration is timed
+"""Interleaved A/B timing of tuning variants (FA_SM100_TUNE=1 builds): every configuration is timed
 `--rounds` times in round-robin order so that clock / thermal drift hits all of them alike; prints
 median and best TFLOP/s per configuration.  Not part of the product.
 
-    python tools/ab.py --shapes c2,c3 --configs 1:128,2:128,3:128,2:64 [--halves 0] [--iters 20] [--rounds 5]
-config = emu:split (for the default generation-5 kernel split 64 selects the speculative-max softmax)."""
+    FA_SM100_TUNE=1 python tools/ab.py --shapes c2,c3 --configs 3:0:1,3:0:0,2:0:1 [--iters 20] [--rounds 5]
+config = emu:spec:fence (exp2 pairs of 8 on the FMA pipe : speculative-max softmax : MMA fence);
+"pack" / "nopack" time the default variant with GQA packing forced on / off."""
 import argparse
 import json
 import statistics
@@ -22,7 +23,6 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--shapes", default="c2,c3")
     ap.add_argument("--configs", default="1:128,2:128,3:128")
-    ap.add_argument("--halves", type=int, default=0)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--rounds", type=int, default=5)
     args = ap.parse_args()
@@ -31,7 +31,8 @@ def main():
 
     ext = load_extension()
     dev = torch.device("cuda:0")
-    cfgs = [tuple(int(x) for x in c.split(":")) for c in args.configs.split(",")]
+    cfgs = [c if c in ("pack", "nopack", "default") else tuple(int(x) for x in c.split(":"))
+            for c in args.configs.split(",")]
     for name in args.shapes.split(","):
         B, Hq, Hkv, Sq, Sk, D, causal, dt = SHAPES[name]
         g = torch.Generator(device=dev).manual_seed(7)
@@ -39,8 +40,8 @@ def main():
         k = torch.randn(B, Hkv, Sk, D, generator=g, device=dev).to(dt)
         v = torch.randn(B, Hkv, Sk, D, generator=g, device=dev).to(dt)
         fl = 4.0 * B * Hq * Sq * Sk * D / (2 if causal else 1)
-        flags = {c: _lib.tune_flags(c[0], c[1], args.halves if args.halves else None) for c in cfgs}
-        flags["v1"] = _lib.FLAG_KERNEL_V1
+        named = {"pack": _lib.FLAG_FORCE_PACK_GQA, "nopack": _lib.FLAG_NO_PACK_GQA, "default": 0}
+        flags = {c: named[c] if isinstance(c, str) else _lib.tune_flags(c[0], bool(c[1]), bool(c[2])) for c in cfgs}
         res = {c: [] for c in flags}
         for c, f in flags.items():
             for _ in range(3):

@@ -1,11 +1,11 @@
 """Record and summarise the in-kernel timeline of CTA 0 (FA_SM100_TUNE builds).  Debug tool.
 
-    python tools/trace_view.py c3nc --emu 0 --split 64
+    FA_SM100_TUNE=1 python tools/trace_view.py c3nc --emu 3
 
-Roles: 0/1 softmax warp 0 of M-tile 0/1, 2 correction warp 0, 3 MMA thread, 4 TMA thread.
-Softmax events: 1 S ready, 2 S loaded, 3 max+scale sent, 4 P part A published, 5 part B published.
-MMA events: 2 prologue issued, 3/4 P1Full seen (tile 0/1), 5/6 tile 0/1 MMAs issued.
-Correction: 7 rescale start, 8 O ready (epilogue), 9 epilogue done.  TMA: 1 Q issued."""
+Roles: 0/1 softmax warp 0 of M-tile 0/1, 2 epilogue warp 0, 3 MMA issuer of M-tile 0, 4 TMA producer.
+Softmax events: 1 S ready, 2 S loaded, 3 first chunk done, 4 P published, 7 lazy rescale.
+MMA events: 2 prologue issued, 3 P seen + stage acquired, 5 batch issued, 23 tile done.
+Epilogue: 8 O ready, 9 tile stored.  Producer: 1 tile start, 6 stage issued."""
 import argparse
 import ctypes
 import json
@@ -27,8 +27,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("shape")
     ap.add_argument("--emu", type=int, default=None)
-    ap.add_argument("--split", type=int, default=None)
-    ap.add_argument("--halves", type=int, default=None)
+    ap.add_argument("--spec", type=int, default=None)
     ap.add_argument("--dump", default=None)
     args = ap.parse_args()
     from flash_attention_cute_b200 import _lib
@@ -42,8 +41,7 @@ def main():
     q = torch.randn(B, Hq, Sq, D, generator=g, device=dev).to(dt)
     k = torch.randn(B, Hkv, Sk, D, generator=g, device=dev).to(dt)
     v = torch.randn(B, Hkv, Sk, D, generator=g, device=dev).to(dt)
-    flags = _lib.tune_flags(0 if args.emu is None else args.emu, 128 if args.split is None else args.split,
-                            None if not args.halves else args.halves)
+    flags = _lib.tune_flags(args.emu, None if args.spec is None else bool(args.spec))
     for _ in range(2):
         ext.flash_attention_fwd(q, k, v, D ** -0.5, causal, flags)
     torch.cuda.synchronize()
