@@ -17,8 +17,10 @@ from pathlib import Path
 PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 ROOT = PKG.parent
-LIB = PKG / "libfa_sm100.so"
-STAMP = PKG / ".libfa_sm100.stamp"
+TUNE = os.environ.get("FA_SM100_TUNE", "") not in ("", "0")
+# the development build lives next to the product library, never in its place
+LIB = PKG / ("libfa_sm100_tune.so" if TUNE else "libfa_sm100.so")
+STAMP = PKG / (".libfa_sm100_tune.stamp" if TUNE else ".libfa_sm100.stamp")
 
 SOURCES = [CSRC / "fa_sm100_host.cu", CSRC / "fa_sm100_selftest.cu"]
 HEADERS = [CSRC / "fa_sm100_fwd.cuh", CSRC / "fa_sm100_sched.cuh", CSRC / "fa_sm100_decode.cuh",
@@ -37,7 +39,7 @@ NVCC_FLAGS = [
 # FA_SM100_TUNE=1 in the environment adds the tuning variants (A/B of exp2 emulation, speculative
 # max, MMA fence; debug timeline) — a development build, never the product (cold build ~25 s
 # without, ~70 s with).
-if os.environ.get("FA_SM100_TUNE", "") not in ("", "0"):
+if TUNE:
     NVCC_FLAGS.insert(5, "-DFA_SM100_TUNE")
 
 
@@ -75,11 +77,11 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         try:
             if not force and is_current():  # another process built it while we waited
                 return LIB
-            tmp = PKG / f".libfa_sm100.{os.getpid()}.tmp.so"
+            tmp = PKG / f".{LIB.stem}.{os.getpid()}.tmp.so"
             cmd = [_nvcc(), *NVCC_FLAGS, "-I", str(ROOT / "include"), "-o", str(tmp), *map(str, SOURCES)]
             proc = subprocess.run(cmd, capture_output=True, text=True)
             log = proc.stdout + proc.stderr
-            (PKG / "build.log").write_text(" ".join(cmd) + "\n" + log)
+            (PKG / ("build_tune.log" if TUNE else "build.log")).write_text(" ".join(cmd) + "\n" + log)
             if proc.returncode != 0:
                 tmp.unlink(missing_ok=True)
                 raise RuntimeError(f"nvcc failed building libfa_sm100.so:\n{log[-4000:]}")

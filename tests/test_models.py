@@ -98,3 +98,57 @@ def test_patched_model_matches_eager_gpu(cuda_device, kind):
     assert _lib.launch_count() - n0 == 4  # per layer: one fused-RoPE launch + one attention launch
     rel = ((got - want).norm() / want.norm()).item()
     assert rel < 2e-2, rel
+
+
+@pytest.mark.gpu
+def test_full_width_llama_layers_patched_vs_eager(cuda_device):
+    """BASELINE config 5 at full width: two Llama-3-8B layers (hidden 4096, 32 q / 8 kv heads of 128,
+    intermediate 14336), random-init bf16, S = 2048 — logits of the patched model against HF eager,
+    and the "free view" after the op (reference models/rope_attn_fwd.py:62,117: O inherits q's
+    [B,S,H,D]-memory strides, so transpose -> reshape -> contiguous copies nothing)."""
+    from transformers import LlamaConfig, LlamaForCausalLM
+    from transformers.models.llama.modeling_llama import LlamaAttention
+
+    import flash_attention_cute_b200.models.rope_attn_fwd as raf
+    from flash_attention_cute_b200 import _lib
+    from models.patch_llama import patch_attn
+
+    cfg = LlamaConfig(hidden_size=4096, num_hidden_layers=2, num_attention_heads=32, num_key_value_heads=8,
+                      intermediate_size=14336, vocab_size=4096, rope_theta=500000.0, max_position_embeddings=4096,
+                      attn_implementation="eager")
+    torch.manual_seed(0)
+    model = LlamaForCausalLM(cfg).to(device=cuda_device, dtype=torch.bfloat16).eval()
+    ids = torch.randint(0, 4096, (2, 2048), generator=torch.Generator().manual_seed(2)).to(cuda_device)
+    with torch.no_grad():
+        eager = model(ids).logits.float()
+        model32 = LlamaForCausalLM(cfg).to(device=cuda_device, dtype=torch.float32).eval()
+        model32.load_state_dict({k: v.float() for k, v in model.state_dict().items()})
+        truth = model32(ids).logits        # same (bf16-valued) weights, fp32 arithmetic
+        del model32
+    original = LlamaAttention.forward
+    real_op = raf.flash_attn_func
+    views = []
+
+    def spying_op(q, k, v, softmax_scale=None, causal=False):
+        o = real_op(q, k, v, softmax_scale=softmax_scale, causal=causal)
+        flat = o.transpose(1, 2).reshape(o.size(0), o.size(2), -1)
+        views.append(o.stride() == q.stride() and flat.is_contiguous() and flat.contiguous().data_ptr() == o.data_ptr())
+        return o
+
+    raf.flash_attn_func = spying_op
+    try:
+        patch_attn()
+        n0 = _lib.launch_count()
+        with torch.no_grad():
+            got = model(ids).logits.float()
+        _lib.check_device(0)
+        assert _lib.launch_count() - n0 == 4  # per layer: fused RoPE + attention
+    finally:
+        LlamaAttention.forward = original
+        raf.flash_attn_func = real_op
+    assert views == [True, True], "the reshape after the op must stay a free view"
+    # both bf16 models against the fp32 evaluation of the same weights: the patched model must be
+    # no further from the truth than HF's own eager bf16 path (plus a quarter)
+    err_ours = ((got - truth).norm() / truth.norm()).item()
+    err_eager = ((eager - truth).norm() / truth.norm()).item()
+    assert err_ours <= 1.25 * err_eager + 1e-3, (err_ours, err_eager)

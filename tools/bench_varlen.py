@@ -60,15 +60,22 @@ def main():
         for n in lens:
             cu.append(cu[-1] + n)
         flops = sum(4.0 * hq * n * n * d / 2 for n in lens)
-        ms = time_fn(lambda: flash_attn_varlen_func(q, k, v, cu, cu, causal=True), args.iters, args.warmup)
+        cu_dev = torch.tensor(cu, dtype=torch.int32, device="cuda")   # device offsets: no host work per call
+        ms = time_fn(lambda: flash_attn_varlen_func(q, k, v, cu_dev, cu_dev, max(lens), max(lens), causal=True),
+                     args.iters, args.warmup)
         row = {"mix": name, "num_seqs": len(lens), "tokens": total, "flops": flops,
                "varlen_ms": ms, "varlen_tflops": flops / ms / 1e9}
         # the same tokens as a padded fixed-length batch (max length), padding FLOPs not counted
         smax = max(lens)
         if len(lens) * smax <= 4 * total and not args.no_comparators:
-            qp = torch.zeros(len(lens), hq, smax, d, device="cuda", dtype=dtype)
-            kp = torch.zeros(len(lens), hkv, smax, d, device="cuda", dtype=dtype)
-            vp = torch.zeros(len(lens), hkv, smax, d, device="cuda", dtype=dtype)
+            if min(lens) == smax:   # equal lengths: the very same tokens as a [B, H, S, D] view
+                qp = q.view(len(lens), smax, hq, d).transpose(1, 2)
+                kp = k.view(len(lens), smax, hkv, d).transpose(1, 2)
+                vp = v.view(len(lens), smax, hkv, d).transpose(1, 2)
+            else:                   # random data of the padded shape (zeros would run cooler and faster)
+                qp = torch.randn(len(lens), hq, smax, d, generator=g, device="cuda").to(dtype)
+                kp = torch.randn(len(lens), hkv, smax, d, generator=g, device="cuda").to(dtype)
+                vp = torch.randn(len(lens), hkv, smax, d, generator=g, device="cuda").to(dtype)
             ms_p = time_fn(lambda: flash_attn_func(qp, kp, vp, causal=True), args.iters, args.warmup)
             row.update(padded_ms=ms_p, padded_tflops_useful=flops / ms_p / 1e9)
         try:
