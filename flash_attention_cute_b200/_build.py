@@ -18,9 +18,12 @@ PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 ROOT = PKG.parent
 TUNE = os.environ.get("FA_SM100_TUNE", "") not in ("", "0")
-# the development build lives next to the product library, never in its place
-LIB = PKG / ("libfa_sm100_tune.so" if TUNE else "libfa_sm100.so")
-STAMP = PKG / (".libfa_sm100_tune.stamp" if TUNE else ".libfa_sm100.stamp")
+# Development builds live next to the product library, never in its place: FA_SM100_TUNE=1 adds the
+# tuning variants; FA_SM100_BUILD_TAG=<tag> with FA_SM100_NVCC_EXTRA="-D..." builds the product
+# sources with other compile-time defaults (e.g. to run the whole parity suite on a candidate).
+TAG = ("_tune" if TUNE else "") + ("_" + os.environ["FA_SM100_BUILD_TAG"] if os.environ.get("FA_SM100_BUILD_TAG") else "")
+LIB = PKG / f"libfa_sm100{TAG}.so"
+STAMP = PKG / f".libfa_sm100{TAG}.stamp"
 
 SOURCES = [CSRC / "fa_sm100_host.cu", CSRC / "fa_sm100_selftest.cu"]
 HEADERS = [CSRC / "fa_sm100_fwd.cuh", CSRC / "fa_sm100_sched.cuh", CSRC / "fa_sm100_decode.cuh",
@@ -41,6 +44,8 @@ NVCC_FLAGS = [
 # without, ~70 s with).
 if TUNE:
     NVCC_FLAGS.insert(5, "-DFA_SM100_TUNE")
+if os.environ.get("FA_SM100_BUILD_TAG") and os.environ.get("FA_SM100_NVCC_EXTRA"):
+    NVCC_FLAGS[5:5] = os.environ["FA_SM100_NVCC_EXTRA"].split()
 
 
 def _nvcc() -> str:
@@ -81,7 +86,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
             cmd = [_nvcc(), *NVCC_FLAGS, "-I", str(ROOT / "include"), "-o", str(tmp), *map(str, SOURCES)]
             proc = subprocess.run(cmd, capture_output=True, text=True)
             log = proc.stdout + proc.stderr
-            (PKG / ("build_tune.log" if TUNE else "build.log")).write_text(" ".join(cmd) + "\n" + log)
+            (PKG / f"build{TAG}.log").write_text(" ".join(cmd) + "\n" + log)
             if proc.returncode != 0:
                 tmp.unlink(missing_ok=True)
                 raise RuntimeError(f"nvcc failed building libfa_sm100.so:\n{log[-4000:]}")

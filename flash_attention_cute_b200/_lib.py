@@ -182,7 +182,12 @@ def load() -> ctypes.CDLL:
         if _lib is not None:
             return _lib
         path = _build.LIB
-        if not _build.is_current():
+        import os as _os
+
+        override = _os.environ.get("FA_SM100_LIB_OVERRIDE")  # development aid: A/B against an older build
+        if override:
+            path = override
+        elif not _build.is_current():
             try:
                 path = _build.build()
             except Exception as exc:

@@ -197,9 +197,9 @@ Variant* pick_variant(int kd, bool bf16, uint32_t flags) {
         if (trace) return variant<D, BF, E, SP, kDefFence, true>();                                    \
         return fence ? variant<D, BF, E, SP, true, false>() : variant<D, BF, E, SP, false, false>();   \
     }
-        FA_V(128, true, 0, false) FA_V(128, true, 2, false) FA_V(128, true, 3, false) FA_V(128, true, 4, false)
+        FA_V(128, true, 0, false) FA_V(128, true, 1, false) FA_V(128, true, 2, false) FA_V(128, true, 3, false) FA_V(128, true, 4, false)
         FA_V(128, true, 3, true)
-        FA_V(64, false, 0, true) FA_V(64, false, 2, true) FA_V(64, false, 3, true) FA_V(64, false, 4, true)
+        FA_V(64, false, 0, true) FA_V(64, false, 1, true) FA_V(64, false, 2, true) FA_V(64, false, 3, true) FA_V(64, false, 4, true)
         FA_V(64, false, 2, false)
 #undef FA_V
     }
@@ -364,8 +364,9 @@ int encode_qkv(fa100::FwdParams* kp, int32_t dtype, int64_t headdim, int group, 
 
 // ---- launch-plan cache: a repeat call with identical arguments (pointers included) skips the
 //      validation, the three cuTensorMapEncodeTiled driver calls and the parameter assembly ----
+std::atomic<uint32_t> g_cache_epoch{1};  // bumped by anything that changes variant selection (debug trace)
 struct CachedLaunch {
-    bool valid = false;
+    uint32_t epoch = 0;  // valid iff == g_cache_epoch
     fa_sm100_fwd_params key;
     fa100::FwdParams kp;  // everything but wait / trace / sched
     Variant* var = nullptr;
@@ -435,7 +436,7 @@ extern "C" int fa_sm100_fwd(const fa_sm100_fwd_params* p, void* stream) {
     if (!p) return fail(FA_SM100_ERR_INVALID_ARGUMENT, "params is NULL");
     DeviceState* st = nullptr;
     CachedLaunch* slot = &g_cache[hash_params(p) % kCacheSlots];
-    if (slot->valid && memcmp(&slot->key, p, sizeof(*p)) == 0) {
+    if (slot->epoch == g_cache_epoch.load(std::memory_order_relaxed) && memcmp(&slot->key, p, sizeof(*p)) == 0) {
         int rc = ready_device(p->device, &st);
         if (rc) return rc;
         DeviceGuard guard(p->device);
@@ -494,7 +495,7 @@ extern "C" int fa_sm100_fwd(const fa_sm100_fwd_params* p, void* stream) {
     slot->kp = kp;
     slot->var = var;
     slot->grid = grid;
-    slot->valid = true;
+    slot->epoch = g_cache_epoch.load(std::memory_order_relaxed);
     return launch_prefill(var, slot->kp, grid, st, stream);
 }
 
@@ -937,5 +938,6 @@ extern "C" void fa_sm100_internal_count_launch(void) { g_launches.fetch_add(1); 
 // only honoured by FA_SM100_TUNE builds (D=128 bf16 / D=64 fp16).  NULL switches tracing off.
 extern "C" void fa_sm100_internal_set_trace(void* device_buffer) {
     g_trace = static_cast<long long*>(device_buffer);
+    g_cache_epoch.fetch_add(1);
 }
 extern "C" int fa_sm100_internal_fail(int code, const char* msg) { return fail(code, "%s", msg); }

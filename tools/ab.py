@@ -31,7 +31,7 @@ def main():
 
     ext = load_extension()
     dev = torch.device("cuda:0")
-    cfgs = [c if c in ("pack", "nopack", "default") else tuple(int(x) for x in c.split(":"))
+    cfgs = [c if not c[0].isdigit() else tuple(int(x) for x in c.split(":"))
             for c in args.configs.split(",")]
     for name in args.shapes.split(","):
         B, Hq, Hkv, Sq, Sk, D, causal, dt = SHAPES[name]

@@ -68,7 +68,7 @@ def main():
     def med(a):
         return float(np.median(a)) if len(a) else float("nan")
 
-    print(f"shape {args.shape} flags emu={args.emu} split={args.split}; events per role:",
+    print(f"shape {args.shape} flags emu={args.emu} spec={args.spec}; events per role:",
           {r: len(ev[r]) for r in ev})
     for role in (0, 1):
         e = ev[role]
