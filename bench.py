@@ -324,14 +324,11 @@ def run_ours(args, w):
     ho = torch.empty(q.shape, dtype=dt).pin_memory()
     dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
     s_in, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
-    # chunks of the rank's block that pipeline H2D | attention | D2H: batch entries, or kv-head
-    # groups when the rank owns a single batch entry (N = 8)
-    if Bl >= 4:
-        chunks = [(slice(b, b + 1), slice(None), slice(None)) for b in range(Bl)]
-    else:
-        per = max(1, Hkvl // max(1, 4 // Bl))
-        chunks = [(slice(b, b + 1), slice(h * G, (h + per) * G), slice(h, h + per))
-                  for b in range(Bl) for h in range(0, Hkvl, per)]
+    # chunks of the rank's block that pipeline H2D | attention | D2H: (batch entry, kv-head range)
+    # pieces, at least eight per rank whatever N is, so the pipeline's fill and drain stay short
+    per = max(1, min(Hkvl, (Bl * Hkvl) // 8))       # kv heads per chunk
+    chunks = [(slice(b, b + 1), slice(h * G, min(Hkvl, h + per) * G), slice(h, min(Hkvl, h + per)))
+              for b in range(Bl) for h in range(0, Hkvl, per)]
 
     def e2e_step():
         cur = torch.cuda.current_stream(dev)
@@ -385,7 +382,24 @@ def run_ours(args, w):
 
     h2d_gbs = copy_probe(dq, hq, s_in)
     d2h_gbs = copy_probe(ho, dq, s_out)
-    link = torch.tensor([h2d_gbs, d2h_gbs], device=dev, dtype=torch.float64)
+    # both directions at once, as the e2e pipeline drives the link
+    barrier()
+    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    cur = torch.cuda.current_stream(dev)
+    a0.record(cur)
+    s_in.wait_stream(cur)
+    s_out.wait_stream(cur)
+    for _ in range(3):
+        with torch.cuda.stream(s_in):
+            dq.copy_(hq, non_blocking=True)
+        with torch.cuda.stream(s_out):
+            ho.copy_(o, non_blocking=True)
+    cur.wait_stream(s_in)
+    cur.wait_stream(s_out)
+    a1.record(cur)
+    torch.cuda.synchronize()
+    bidir_gbs = 3 * (hq.numel() + ho.numel()) * hq.element_size() / (a0.elapsed_time(a1) * 1e-3) / 1e9
+    link = torch.tensor([h2d_gbs, d2h_gbs, bidir_gbs], device=dev, dtype=torch.float64)
     link_min = link.clone()
     if world > 1:
         dist.all_reduce(link, op=dist.ReduceOp.SUM)
@@ -461,7 +475,10 @@ def run_ours(args, w):
                     "steps": e2e_steps, "result_matches_device_run": bool(e2e_ok),
                     "host_link": {"h2d_gbs_sum": float(link[0]), "d2h_gbs_sum": float(link[1]),
                                   "h2d_gbs_min_rank": float(link_min[0]), "d2h_gbs_min_rank": float(link_min[1]),
-                                  "note": "pinned-memory copies alone, all ranks at once, one direction at a time"},
+                                  "both_directions_gbs_sum": float(link[2]), "both_directions_gbs_min_rank": float(link_min[2]),
+                                  "e2e_bytes_over_time_gbs": (h2d + d2h) / (e2e_ms / e2e_steps * 1e-3) / 1e9,
+                                  "note": "pinned-memory copies alone (no compute), all ranks at once: each direction by itself, then both together"},
+                    "chunks_per_rank": len(chunks),
                     "numa": numa},
             "gpu_launches": int(launches),
             "clocks": clk.summary(),
