@@ -322,42 +322,56 @@ def run_ours(args, w):
     # ---- end to end through the public API with HOST buffers (pinned), copies inside the timing ----
     hq, hk, hv = (x.cpu().pin_memory() for x in (q, k, v))
     ho = torch.empty(q.shape, dtype=dt).pin_memory()
-    dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+    # two sets of device staging buffers: the copies of step k+1 run under the attention and the
+    # read-back of step k (a serving pipeline); every copy of every step is inside the timed region
+    dq, dk, dv = [torch.empty_like(q), torch.empty_like(q)], [torch.empty_like(k), torch.empty_like(k)], \
+        [torch.empty_like(v), torch.empty_like(v)]
     s_in, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
     # chunks of the rank's block that pipeline H2D | attention | D2H: (batch entry, kv-head range)
     # pieces, at least eight per rank whatever N is, so the pipeline's fill and drain stay short
     per = max(1, min(Hkvl, (Bl * Hkvl) // 8))       # kv heads per chunk
     chunks = [(slice(b, b + 1), slice(h * G, min(Hkvl, h + per) * G), slice(h, min(Hkvl, h + per)))
               for b in range(Bl) for h in range(0, Hkvl, per)]
+    consumed = [[None] * len(chunks), [None] * len(chunks)]   # attention of (set, chunk) has read its inputs
 
-    def e2e_step():
+    def e2e_step(step: int):
         cur = torch.cuda.current_stream(dev)
-        s_in.wait_stream(cur)
-        s_out.wait_stream(cur)
-        for bs, qh, kh in chunks:
+        j = step & 1
+        for c, (bs, qh, kh) in enumerate(chunks):
             with torch.cuda.stream(s_in):
-                dq[bs, qh].copy_(hq[bs, qh], non_blocking=True)
-                dk[bs, kh].copy_(hk[bs, kh], non_blocking=True)
-                dv[bs, kh].copy_(hv[bs, kh], non_blocking=True)
+                if consumed[j][c] is not None:
+                    s_in.wait_event(consumed[j][c])   # the step before last is done with this staging piece
+                dq[j][bs, qh].copy_(hq[bs, qh], non_blocking=True)
+                dk[j][bs, kh].copy_(hk[bs, kh], non_blocking=True)
+                dv[j][bs, kh].copy_(hv[bs, kh], non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record(s_in)
             cur.wait_event(ev)
-            ob = flash_attn_func(dq[bs, qh], dk[bs, kh], dv[bs, kh], causal=causal)
+            ob = flash_attn_func(dq[j][bs, qh], dk[j][bs, kh], dv[j][bs, kh], causal=causal)
             ev2 = torch.cuda.Event()
             ev2.record(cur)
+            consumed[j][c] = ev2
             with torch.cuda.stream(s_out):
                 s_out.wait_event(ev2)
                 ho[bs, qh].copy_(ob, non_blocking=True)
                 ob.record_stream(s_out)
+
+    def e2e_drain():
+        cur = torch.cuda.current_stream(dev)
+        cur.wait_stream(s_in)
         cur.wait_stream(s_out)
 
     e2e_steps = max(2, min(args.steps, 10))
-    for _ in range(2):
-        e2e_step()
+    s_in.wait_stream(torch.cuda.current_stream(dev))
+    s_out.wait_stream(torch.cuda.current_stream(dev))
+    for i in range(2):
+        e2e_step(i)
+    e2e_drain()
     barrier()
     e0.record()
-    for _ in range(e2e_steps):
-        e2e_step()
+    for i in range(e2e_steps):
+        e2e_step(i)
+    e2e_drain()       # the last read-back is inside the timed region
     e1.record()
     torch.cuda.synchronize()
     e2e_ms = max_over_ranks(e0.elapsed_time(e1))
@@ -380,8 +394,8 @@ def run_ours(args, w):
         torch.cuda.synchronize()
         return 3 * src.numel() * src.element_size() / (a.elapsed_time(b) * 1e-3) / 1e9
 
-    h2d_gbs = copy_probe(dq, hq, s_in)
-    d2h_gbs = copy_probe(ho, dq, s_out)
+    h2d_gbs = copy_probe(dq[0], hq, s_in)
+    d2h_gbs = copy_probe(ho, dq[0], s_out)
     # both directions at once, as the e2e pipeline drives the link
     barrier()
     a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -391,7 +405,7 @@ def run_ours(args, w):
     s_out.wait_stream(cur)
     for _ in range(3):
         with torch.cuda.stream(s_in):
-            dq.copy_(hq, non_blocking=True)
+            dq[0].copy_(hq, non_blocking=True)
         with torch.cuda.stream(s_out):
             ho.copy_(o, non_blocking=True)
     cur.wait_stream(s_in)
