@@ -269,3 +269,25 @@ def test_c4_sweep_sizes(cuda_device, S, Hkv, causal):
         assert_close(out[:, hs].index_select(2, rows), ref, torch.float16, f"C4 S=32K Hkv={Hkv}")
     else:
         _sampled_units_close(out, q, k, v, causal, torch.float16, [(0, 0), (B - 1, Hkv - 1)], f"C4 S={S} Hkv={Hkv}")
+
+
+def test_prefill_is_graph_capturable(cuda_device):
+    """The forward launch allocates nothing and synchronises nothing: it can be captured into a CUDA
+    graph and replayed (the captured launch bakes in one slot of the scheduler-counter ring)."""
+    from flash_attention import flash_attn_func
+
+    q, k, v = make_qkv_fast(2, 8, 2, 700, 700, 128, torch.bfloat16, 31, cuda_device)
+    eager = flash_attn_func(q, k, v, causal=True)
+    torch.cuda.synchronize()
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            out = flash_attn_func(q, k, v, causal=True)
+    for _ in range(3):
+        out.zero_()
+        g.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(out, eager)
+    from flash_attention_cute_b200 import _lib
+    _lib.check_device(0)

@@ -23,6 +23,9 @@ SHAPES = {
     "c4s4k": (8, 14, 2, 4096, 4096, 64, True, torch.float16),
     "c4s32k": (1, 14, 2, 32768, 32768, 64, True, torch.float16),
     "c4s4knc": (8, 14, 2, 4096, 4096, 64, False, torch.float16),
+    "s512": (128, 32, 8, 512, 512, 128, True, torch.bfloat16),      # many short work tiles per CTA
+    "s1k": (64, 32, 8, 1024, 1024, 128, True, torch.bfloat16),
+    "c4s512": (64, 14, 2, 512, 512, 64, True, torch.float16),
 }
 
 
