@@ -123,7 +123,7 @@ __device__ __forceinline__ bool mbar_wait(uint32_t bar, uint32_t parity, const W
     uint64_t t0 = 0;
     uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity)) {
-        if ((++spins & 0x3ffu) == 0) {
+        if ((++spins & 0x3fu) == 0) {  // a failed try_wait has slept for microseconds in hardware: ~1 ms between checks
             if (*reinterpret_cast<volatile unsigned int*>(ctx.status) != 0u) {  // someone aborted
                 atomicOr(ctx.status + 3, 1u << (code & 31u));  // leave a trace of every blocked wait site
                 return false;

@@ -291,3 +291,42 @@ def test_prefill_is_graph_capturable(cuda_device):
         assert torch.equal(out, eager)
     from flash_attention_cute_b200 import _lib
     _lib.check_device(0)
+
+
+def test_watchdog_abort_is_contained(cuda_device):
+    """a wait that gives up must not turn later waits into no-ops.  With the
+    watchdog at 1 ms a work tile of 524288 keys (≈ 6 ms) makes the epilogue's wait for its row sums time out
+    legitimately: the launch must end by itself, report through fa_sm100_check_device, make every
+    further entry-point call fail loudly until it is cleared, and leave the device healthy."""
+    import ctypes
+
+    from flash_attention import flash_attn_func
+    from flash_attention_cute_b200 import _lib
+    from flash_attention_cute_b200.load_cpp_extention import fill_params
+
+    lib = _lib.load()
+    qs, ks, vs = make_qkv_fast(1, 4, 4, 256, 256, 128, torch.bfloat16, 77, cuda_device)
+    want = flash_attn_func(qs, ks, vs, causal=True)
+    _lib.check_device(0)
+    q, k, v = make_qkv_fast(1, 2, 2, 256, 524288, 128, torch.bfloat16, 78, cuda_device)
+    lib.fa_sm100_set_watchdog_ms(1)
+    try:
+        flash_attn_func(q, k, v, causal=False)          # asynchronous: returns, then times out in the kernel
+        flash_attn_func(qs, ks, vs, causal=True)        # queued behind it: must do nothing
+        torch.cuda.synchronize()
+        # the entry points refuse to launch while the condition is pending (host-mapped status word)
+        o = torch.empty_like(qs)
+        p = fill_params(qs, ks, vs, o, 128 ** -0.5, True)
+        rc = lib.fa_sm100_fwd(ctypes.byref(p), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+        assert rc == 4 and "fa_sm100_check_device" in _lib.last_error()
+        with pytest.raises(RuntimeError, match="watchdog fired"):
+            _lib.check_device(0)
+    finally:
+        lib.fa_sm100_set_watchdog_ms(2000)
+    _lib.check_device(0)                                 # cleared: healthy again
+    again = flash_attn_func(qs, ks, vs, causal=True)
+    _lib.check_device(0)
+    assert torch.equal(again, want)
+    full = flash_attn_func(q, k, v, causal=False)       # the long tile itself, with the default watchdog
+    _lib.check_device(0)
+    assert torch.isfinite(full.float()).all()
