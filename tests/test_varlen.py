@@ -225,3 +225,38 @@ def test_varlen_device_offsets_strided_views_and_no_leak():
             o3 = flash_attn_varlen_func(q, k, v, cu_q, cu_k, causal=causal)
             assert torch.equal(o2[cu_q[1]:cu_q[2]], o3[cu_q[1]:cu_q[2]])
     _lib.check_device(0)
+
+
+@pytest.mark.gpu
+def test_varlen_thousands_of_sequences_and_keyless_queries():
+    """More sequences than the plan kernel ranks (> 2048: given order is kept), lengths 0 … 300 with
+    Sq != Sk, some sequences with queries but no keys (their rows must come back as zeros)."""
+    from flash_attention import flash_attn_func, flash_attn_varlen_func
+
+    n = 3000
+    gen = torch.Generator().manual_seed(4400)
+    lens_q = torch.randint(0, 301, (n,), generator=gen).tolist()
+    lens_k = torch.randint(0, 301, (n,), generator=gen).tolist()
+    for i in range(0, n, 97):
+        lens_k[i] = 0                      # queries without keys
+        lens_q[i] = max(lens_q[i], 3)
+    q, k, v, cu_q, cu_k = _packed(lens_q, lens_k, 8, 2, 64, torch.float16, 4401)
+    cq = torch.tensor(cu_q, dtype=torch.int32, device="cuda")
+    ck = torch.tensor(cu_k, dtype=torch.int32, device="cuda")
+    o = flash_attn_varlen_func(q, k, v, cq, ck, 300, 300, causal=False)
+    _lib.check_device(0)
+    assert torch.isfinite(o.float()).all()
+    for i in list(range(0, n, 97))[:8]:
+        assert not o[cu_q[i]:cu_q[i + 1]].any(), f"sequence {i} has no keys: zeros expected"
+    for i in (1, 2, 500, 1499, 2047, 2048, 2999):
+        sq, sk = lens_q[i], lens_k[i]
+        if sq == 0 or sk == 0:
+            continue
+        qi = q[cu_q[i]:cu_q[i + 1]].transpose(0, 1).unsqueeze(0)
+        ki = k[cu_k[i]:cu_k[i + 1]].transpose(0, 1).unsqueeze(0)
+        vi = v[cu_k[i]:cu_k[i + 1]].transpose(0, 1).unsqueeze(0)
+        oi = o[cu_q[i]:cu_q[i + 1]].transpose(0, 1).unsqueeze(0)
+        ref = eager_attention(qi.cpu(), ki.cpu(), vi.cpu(), None, False)
+        assert_close(oi.cpu(), ref.float(), torch.float16, f"seq {i} ({sq} x {sk})")
+        if sq > 1:
+            assert torch.equal(flash_attn_func(qi, ki, vi, causal=False), oi)
