@@ -45,6 +45,8 @@ EXPORTED_SYMBOLS = (
     "fa_sm100_fwd",
     "fa_sm100_fwd_decode",
     "fa_sm100_decode_plan",
+    "fa_sm100_fwd_decode_static",
+    "fa_sm100_static_scratch_bytes",
     "fa_sm100_paged_decode_plan",
     "fa_sm100_fwd_decode_paged",
     "fa_sm100_varlen_workspace_bytes",
@@ -222,6 +224,10 @@ def load() -> ctypes.CDLL:
         lib.fa_sm100_decode_plan.restype = c_int32
         lib.fa_sm100_fwd_decode.argtypes = [POINTER(FwdParams), c_void_p, c_int64, c_void_p]
         lib.fa_sm100_fwd_decode.restype = c_int32
+        lib.fa_sm100_fwd_decode_static.argtypes = [POINTER(FwdParams), c_void_p]
+        lib.fa_sm100_fwd_decode_static.restype = c_int32
+        lib.fa_sm100_static_scratch_bytes.argtypes = []
+        lib.fa_sm100_static_scratch_bytes.restype = c_int64
         lib.fa_sm100_paged_decode_plan.argtypes = [POINTER(PagedDecodeParams), POINTER(c_int32), POINTER(c_int32),
                                                    POINTER(c_int64)]
         lib.fa_sm100_paged_decode_plan.restype = c_int32

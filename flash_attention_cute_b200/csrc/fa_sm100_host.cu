@@ -826,6 +826,115 @@ extern "C" int fa_sm100_fwd_decode_paged(const fa_sm100_paged_decode_params* p, 
 }
 
 // ------------------------------------------------------------------------------------------------
+// Split-KV decode without any allocation: fa_sm100_fwd_decode_static
+// ------------------------------------------------------------------------------------------------
+// The split partials and the per-unit arrival counters of the decode kernel live in a file-scope
+// device array instead of a caller workspace plus the cudaMalloc'ed counter ring, so this entry
+// point (and its set-up) never allocates.  Every device that loads the library holds the array
+// until the process exits.  In host code `g_static_scratch` is only a stand-in for the symbol:
+// the device address comes from cudaGetSymbolAddress, once per device with that device current.
+namespace {
+
+constexpr int64_t kStaticScratchBytes = FA_SM100_STATIC_SCRATCH_BYTES;
+constexpr int64_t kStaticCounterBytes = 2048;  // 512 arrival counters in front of the partials
+static_assert(kStaticCounterBytes % 256 == 0, "partials must stay 256-byte aligned");
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+struct StaticDevice {
+    std::mutex mu;
+    unsigned char* scratch = nullptr;  // device address of g_static_scratch on this device
+    int cc_major = 0, num_sms = 0;
+};
+StaticDevice g_static_dev[kMaxDevices];
+
+// Caller holds a DeviceGuard for `device` (the symbol is resolved for the current device).
+int static_device(int device, StaticDevice** out) {
+    StaticDevice* sd = &g_static_dev[device];
+    std::lock_guard<std::mutex> lock(sd->mu);
+    if (!sd->scratch) {
+        cudaError_t e = cudaDeviceGetAttribute(&sd->cc_major, cudaDevAttrComputeCapabilityMajor, device);
+        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sd->num_sms, cudaDevAttrMultiProcessorCount, device);
+        if (e != cudaSuccess) return fail(FA_SM100_ERR_CUDA, "cudaDeviceGetAttribute: %s", cudaGetErrorString(e));
+        unsigned char* ptr = nullptr;
+        e = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_static_scratch);
+        if (e != cudaSuccess || !ptr)
+            return fail(FA_SM100_ERR_CUDA, "cudaGetSymbolAddress(static scratch) on device %d: %s", device,
+                        cudaGetErrorString(e));
+        sd->scratch = ptr;
+    }
+    *out = sd;
+    return FA_SM100_OK;
+}
+
+}  // namespace
+
+extern "C" int64_t fa_sm100_static_scratch_bytes(void) { return kStaticScratchBytes; }
+
+extern "C" int fa_sm100_fwd_decode_static(const fa_sm100_fwd_params* p, void* stream) {
+    if (!p) return fail(FA_SM100_ERR_INVALID_ARGUMENT, "params is NULL");
+    if (p->device < 0 || p->device >= kMaxDevices)
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT, "bad device ordinal %d", p->device);
+    DeviceGuard guard(p->device);
+    StaticDevice* sd = nullptr;
+    int rc = static_device(p->device, &sd);
+    if (rc) return rc;
+    if (sd->cc_major != 10)
+        return fail(FA_SM100_ERR_UNSUPPORTED_DEVICE,
+                    "fa_sm100 needs an sm_100 (B200) GPU; device %d is sm_%dx — there is no fallback",
+                    p->device, sd->cc_major);
+    DecodePlan dp;
+    rc = decode_plan(p, sd->num_sms, &dp);  // the same split as fa_sm100_fwd_decode: bit-equal results
+    if (rc) return rc;
+    const int64_t need = dp.ml_bytes + dp.o_bytes;
+    if (need > kStaticScratchBytes - kStaticCounterBytes)
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT,
+                    "decode split needs %lld bytes of scratch, the static array holds %lld "
+                    "(FA_SM100_STATIC_SCRATCH_BYTES minus %lld of counters); use fa_sm100_fwd_decode with a workspace",
+                    (long long)need, (long long)(kStaticScratchBytes - kStaticCounterBytes),
+                    (long long)kStaticCounterBytes);
+    if (dp.nsplit > 1 && int64_t(dp.units) * 4 > kStaticCounterBytes)
+        return fail(FA_SM100_ERR_INVALID_ARGUMENT, "decode split with %d units exceeds the %lld static counters",
+                    dp.units, (long long)(kStaticCounterBytes / 4));
+
+    DecodeVariant* var = pick_decode<false>(dp.kd, p->dtype == FA_SM100_BF16);
+    cudaError_t attr_err = cudaSuccess;
+    std::call_once(var->attr_once[p->device], [&] {
+        attr_err = cudaFuncSetAttribute(reinterpret_cast<const void*>(var->fn),
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, var->smem_bytes);
+    });
+    if (attr_err != cudaSuccess)
+        return fail(FA_SM100_ERR_CUDA, "cudaFuncSetAttribute(decode): %s", cudaGetErrorString(attr_err));
+
+    fa100::decode::DecodeParams kp;
+    memset(&kp, 0, sizeof(kp));
+    kp.q = p->q; kp.k = p->k; kp.v = p->v; kp.o = p->o;
+    kp.batch = int(p->batch); kp.heads_kv = int(p->heads_kv); kp.group = dp.group;
+    kp.seqlen_k = int(p->seqlen_kv); kp.headdim = int(p->headdim);
+    kp.q_sb = p->q_strides[0]; kp.q_sh = p->q_strides[1];
+    kp.k_sb = p->k_strides[0]; kp.k_sh = p->k_strides[1]; kp.k_ss = p->k_strides[2];
+    kp.v_sb = p->v_strides[0]; kp.v_sh = p->v_strides[1]; kp.v_ss = p->v_strides[2];
+    kp.o_sb = p->o_strides[0]; kp.o_sh = p->o_strides[1];
+    kp.scale_log2 = p->softmax_scale * 1.4426950408889634f;
+    kp.nsplit = dp.nsplit;
+    kp.chunk = dp.chunk;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (dp.nsplit > 1) {
+        // The array keeps whatever the last call left in it.  Partials are written before they are
+        // read; the arrival counters must start at zero, so they are cleared in stream order.
+        kp.counters = reinterpret_cast<int*>(sd->scratch);
+        kp.part_ml = reinterpret_cast<float*>(sd->scratch + kStaticCounterBytes);
+        kp.part_o = reinterpret_cast<float*>(sd->scratch + kStaticCounterBytes + dp.ml_bytes);
+        cudaError_t e = cudaMemsetAsync(kp.counters, 0, size_t(dp.units) * sizeof(int), s);
+        if (e != cudaSuccess) return fail(FA_SM100_ERR_CUDA, "cudaMemsetAsync(static counters): %s", cudaGetErrorString(e));
+    }
+    var->fn<<<dim3(dp.units * dp.nsplit), dim3(fa100::decode::kThreads), var->smem_bytes, s>>>(kp);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(FA_SM100_ERR_CUDA, "decode kernel launch: %s", cudaGetErrorString(e));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return FA_SM100_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
 // Fused RoPE on q and k: fa_sm100_rope.cuh
 // ------------------------------------------------------------------------------------------------
 extern "C" int fa_sm100_rope(const fa_sm100_rope_params* p, void* stream) {

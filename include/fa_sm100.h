@@ -113,6 +113,28 @@ int fa_sm100_decode_plan(const fa_sm100_fwd_params* params, int32_t* nsplit, int
 int fa_sm100_fwd_decode(const fa_sm100_fwd_params* params, void* workspace, int64_t workspace_bytes,
                         void* stream);
 
+/* ---- Decode (seqlen_q == 1) that allocates nothing -----------------------------------------------
+ * No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that
+ * forbid it).  Same params, validation, split plan, kernel and results (bit-equal) as
+ * fa_sm100_fwd_decode, but the split partials and the per-unit arrival counters live in a
+ * file-scope device array of FA_SM100_STATIC_SCRATCH_BYTES inside the library instead of a caller
+ * workspace and the library's allocated counter ring.  Neither the call nor its once-per-device
+ * set-up (cudaGetSymbolAddress with that device current) calls cudaMalloc, cudaFree or any
+ * allocating routine; every GPU that loads the library holds the array until the process exits.
+ * A split that needs more than the array holds (fa_sm100_decode_plan's workspace_bytes >
+ * FA_SM100_STATIC_SCRATCH_BYTES - 2048) is FA_SM100_ERR_INVALID_ARGUMENT with the sizes in
+ * fa_sm100_last_error — with the one-wave plan on a 148-SM B200 the largest request is 2.46 MB,
+ * so the limit only binds on parts with more than 251 SMs.  All calls on a device share the
+ * array, which keeps the last call's contents: the counters are cleared in stream order before
+ * every launch, the partials are written before they are read, so calls ordered on one stream
+ * (or by events) are safe — calls that OVERLAP on the GPU (different streams, no ordering) race
+ * on it and must use fa_sm100_fwd_decode with separate workspaces.  This entry point does not
+ * consult or set the device's sticky watchdog status (the decode kernel has no in-kernel waits). */
+#define FA_SM100_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)
+int fa_sm100_fwd_decode_static(const fa_sm100_fwd_params* params, void* stream);
+int64_t fa_sm100_static_scratch_bytes(void);
+
 /* ---- Paged-KV decode (seqlen_q == 1) -----------------------------------------------------------------
  * SURVEY §8(f) rank 4; "paged KV cache" is a TODO of the reference (README.md:21), so the contract
  * is the contiguous decode above applied to the keys a block table names: sequence b owns
