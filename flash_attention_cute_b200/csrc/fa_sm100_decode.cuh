@@ -23,6 +23,13 @@
 //   * the four warps merge (m, l, O) through shared memory; with nsplit > 1 the CTA writes its
 //     partial to the workspace and the last CTA of a unit to arrive (one atomic counter per unit)
 //     merges the splits and writes O — one launch, no second kernel.
+//   * paged KV with per-sequence lengths (fa_decode_flat_sm100): the host cannot size a split per
+//     sequence (the lengths are device data), so the CTAs of one wave share the FLATTENED key space
+//     instead: every (batch, kv-head) unit owns ceil(len / 64) blocks of 64 keys, laid end to end,
+//     and CTA i takes blocks [i·W, (i+1)·W) of that line, whichever units they belong to.  A CTA
+//     walks its range unit by unit ("segments"); a segment that covers its unit writes O, any
+//     other writes a partial, and the last CTA of a unit to arrive merges.  Every CTA streams the
+//     same number of bytes however ragged the batch is.
 #pragma once
 
 #include <cuda_bf16.h>
@@ -40,6 +47,8 @@ constexpr int kTileKeys = 16;   // keys per warp tile
 constexpr int kStages = 3;      // cp.async ring depth per warp
 constexpr int kRows = 16;       // MMA M: q heads of one kv group (G <= 16), rest zero
 constexpr float kNegBig = -1.0e30f;  // finite stand-in for -inf in the running max
+constexpr int kFlatBlock = kWarps * kTileKeys;  // 64 keys: granularity of the flattened key space
+constexpr int kFlatMaxBatch = 2048;  // sequences whose prefix sums a CTA keeps in shared memory
 
 struct DecodeParams {
     const void* q;
@@ -64,6 +73,10 @@ struct DecodeParams {
     int64_t bt_stride;
     int64_t k_sp, v_sp;       // element stride between pages
     int page_size;            // multiple of kTileKeys
+    int page_shift;           // log2(page_size) when it is a power of two, else -1
+    // flattened key space (fa_decode_flat_sm100): part_o / part_ml hold 2 slots per CTA (its
+    // first and its last segment), counters one int per CTA
+    int flat_min_blocks;      // smallest range of a CTA, in blocks of kFlatBlock keys
 };
 
 template <int kD>
@@ -134,26 +147,81 @@ __device__ __forceinline__ float fast_exp2(float x) {
     return y;
 }
 
+
+// ---- one warp copies one 16-key K tile and V tile into a ring stage --------------------------------
+// The kernels issue 48 % of the cycles they are resident, two warps to a scheduler: instructions
+// count, and 64-bit address arithmetic per 16-byte copy was 40 % of them.  Everything that does
+// not change from tile to tile is computed once per kernel here: lane l copies chunk c = l % kChunks
+// of rows l / kChunks + j · (32 / kChunks); the shared-memory offsets are XOR-swizzled per row.
+template <int kD>
+struct TileCopy {
+    static constexpr int kChunks = kD / 8;                      // 16-byte chunks per row
+    static constexpr int kCopies = kTileKeys * kChunks / 32;    // cp.async per lane per K (or V) tile
+    static constexpr int kRowStep = 32 / kChunks;               // rows between a lane's copies
+    int64_t k_lane, v_lane;   // BYTE offset of the lane's first copy inside a tile
+    int64_t k_step, v_step;   // byte offset between its copies
+    uint32_t soff[kCopies];   // byte offsets inside the stage's K (or V) tile
+    int row, chunk;           // first row and chunk of the lane
+
+    __device__ __forceinline__ void init(const DecodeParams& p, int lane) {
+        using L = Smem<kD>;
+        row = lane / kChunks;
+        chunk = lane - row * kChunks;
+        k_lane = (row * p.k_ss + chunk * 8) * 2;
+        v_lane = (row * p.v_ss + chunk * 8) * 2;
+        k_step = kRowStep * p.k_ss * 2;
+        v_step = kRowStep * p.v_ss * 2;
+#pragma unroll
+        for (int j = 0; j < kCopies; ++j) {
+            const int r = row + j * kRowStep;
+            soff[j] = r * L::kRowBytes + ((chunk ^ (r & 7)) << 4);
+        }
+    }
+    // kt / vt: row 0 of the tile (head and page applied); rows >= valid_rows and chunks >= D / 8
+    // are zero-filled.  `safe` is any mapped address (zero-size copies still carry one).
+    template <typename T>
+    __device__ __forceinline__ void copy(uint32_t dst, const T* kt, const T* vt, int valid_rows, int D,
+                                         const T* safe) const {
+        using L = Smem<kD>;
+        const char* ks = reinterpret_cast<const char*>(kt) + k_lane;
+        const char* vs = reinterpret_cast<const char*>(vt) + v_lane;
+        if (valid_rows >= kTileKeys && D == kD) {
+#pragma unroll
+            for (int j = 0; j < kCopies; ++j) {
+                cp_async16(dst + soff[j], ks, true);
+                cp_async16(dst + L::kTileBytes + soff[j], vs, true);
+                ks += k_step;
+                vs += v_step;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < kCopies; ++j) {
+                const bool ok = row + j * kRowStep < valid_rows && chunk * 8 < D;
+                cp_async16(dst + soff[j], ok ? ks : reinterpret_cast<const char*>(safe), ok);
+                cp_async16(dst + L::kTileBytes + soff[j], ok ? vs : reinterpret_cast<const char*>(safe), ok);
+                ks += k_step;
+                vs += v_step;
+            }
+        }
+    }
+};
+
+// ---- one key range of one (batch, kv-head) unit ---------------------------------------------------
+// All four warps stream keys [key_begin, key_end) of unit (b, kvh) — key_begin a multiple of 16 —
+// and leave their (m, l, O) triples in the merge buffers of shared memory (which overlay the ring:
+// the ring is idle on entry and idle again on return).  Ends with a __syncthreads().
 template <int kD, bool kBf16, bool kPaged>
-__global__ void __launch_bounds__(kThreads, 2)
-fa_decode_sm100(const DecodeParams p) {
+__device__ __forceinline__ void attend_range(const DecodeParams& p, uint8_t* smem, int b, int kvh,
+                                             int key_begin, int key_end) {
     using L = Smem<kD>;
-    constexpr int kChunks = kD / 8;        // 16-byte chunks per row
-    constexpr int kCopies = kTileKeys * kChunks / 32;  // cp.async per lane per K (or V) tile
+    using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
     constexpr int kKSteps = kD / 16;       // MMA k-steps of Q·Kᵀ
     constexpr int kNBlocks = kD / 8;       // MMA n-blocks of P·V
-    extern __shared__ __align__(128) uint8_t smem[];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int unit = blockIdx.x / p.nsplit, split = blockIdx.x - unit * p.nsplit;
-    const int b = unit / p.heads_kv, kvh = unit - b * p.heads_kv;
     const int G = p.group, D = p.headdim;
-    const int key_begin = split * p.chunk;
-    const int seqlen = kPaged ? p.seqlens[b] : p.seqlen_k;
-    const int key_end = min(seqlen, key_begin + p.chunk);
     const int ntiles = key_end > key_begin ? (key_end - key_begin + kTileKeys - 1) / kTileKeys : 0;
 
-    using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
     const T* kbase = reinterpret_cast<const T*>(p.k) + (kPaged ? 0 : b * p.k_sb) + kvh * p.k_sh;
     const T* vbase = reinterpret_cast<const T*>(p.v) + (kPaged ? 0 : b * p.v_sb) + kvh * p.v_sh;
     const uint32_t ring = smem_addr(smem) + warp * L::kWarpBytes;
@@ -163,11 +231,14 @@ fa_decode_sm100(const DecodeParams p) {
     const int32_t* bt = kPaged ? p.block_table + b * p.bt_stride : nullptr;
     int phys_pref = 0;
     if constexpr (kPaged) {
-        if (warp < ntiles) phys_pref = __ldg(bt + (key_begin + warp * kTileKeys) / p.page_size);
+        const int key0 = key_begin + warp * kTileKeys;
+        if (warp < ntiles) phys_pref = __ldg(bt + (p.page_shift >= 0 ? key0 >> p.page_shift : key0 / p.page_size));
     }
 
     // ---- per-warp cp.async ring ----
-    auto issue_tile = [&](int t) {  // t: tile index inside the chunk (this warp's), may be >= ntiles
+    TileCopy<kD> tc;
+    tc.init(p, lane);
+    auto issue_tile = [&](int t) {  // t: tile index inside the range (this warp's), may be >= ntiles
         if (t < ntiles) {
             const int stage = (t / kWarps) % kStages;
             const uint32_t dst = ring + stage * L::kStageBytes;
@@ -176,21 +247,16 @@ fa_decode_sm100(const DecodeParams p) {
             const T* vb = vbase;
             int row0 = key0;  // token index of the tile's first row relative to kb / vb
             if constexpr (kPaged) {
-                const int pg = key0 / p.page_size;
-                row0 = key0 - pg * p.page_size;
+                row0 = p.page_shift >= 0 ? key0 & (p.page_size - 1) : key0 % p.page_size;
                 kb += static_cast<int64_t>(phys_pref) * p.k_sp;
                 vb += static_cast<int64_t>(phys_pref) * p.v_sp;
-                if (t + kWarps < ntiles) phys_pref = __ldg(bt + (key0 + kWarps * kTileKeys) / p.page_size);
+                if (t + kWarps < ntiles) {
+                    const int keyn = key0 + kWarps * kTileKeys;
+                    phys_pref = __ldg(bt + (p.page_shift >= 0 ? keyn >> p.page_shift : keyn / p.page_size));
+                }
             }
-#pragma unroll
-            for (int j = 0; j < kCopies; ++j) {
-                const int i = lane + 32 * j;
-                const int row = i / kChunks, c = i - row * kChunks;
-                const bool ok = key0 + row < key_end && c * 8 < D;
-                const uint32_t off = row * L::kRowBytes + ((c ^ (row & 7)) << 4);
-                cp_async16(dst + off, ok ? kb + static_cast<int64_t>(row0 + row) * p.k_ss + c * 8 : kbase, ok);
-                cp_async16(dst + L::kTileBytes + off, ok ? vb + static_cast<int64_t>(row0 + row) * p.v_ss + c * 8 : vbase, ok);
-            }
+            tc.copy(dst, kb + static_cast<int64_t>(row0) * p.k_ss, vb + static_cast<int64_t>(row0) * p.v_ss,
+                    key_end - key0, D, kbase);
         }
         cp_async_commit();  // always commit: the wait below counts groups
     };
@@ -246,7 +312,7 @@ fa_decode_sm100(const DecodeParams p) {
                 mma_16816<kBf16>(s[1], qa[ks], b2, b3);
             }
         }
-        // mask keys past the end of this chunk (only the last tile can have them)
+        // mask keys past the end of this range (only the last tile can have them)
         const int key0 = key_begin + t * kTileKeys;
         if (key0 + kTileKeys > key_end) {
 #pragma unroll
@@ -325,9 +391,18 @@ fa_decode_sm100(const DecodeParams p) {
     }
     __syncthreads();
 
+}
+
+// Combine the four warps' triples left by attend_range and either write O of unit (b, kvh)
+// (final: the range was the whole unit) or the partial into workspace slot `slot`.
+template <int kD, bool kBf16>
+__device__ __forceinline__ void write_range(const DecodeParams& p, const uint8_t* smem, int b, int kvh,
+                                            bool final, int64_t slot) {
+    using L = Smem<kD>;
+    const int G = p.group, D = p.headdim;
     const float* all_o = reinterpret_cast<const float*>(smem + L::kMergeO);
     const float* all_ml = reinterpret_cast<const float*>(smem + L::kMergeML);
-    const int64_t part_base = (static_cast<int64_t>(unit) * p.nsplit + split) * kRows;
+    const int64_t part_base = slot * kRows;
     for (int idx = threadIdx.x; idx < G * kD; idx += kThreads) {
         const int row = idx / kD, d = idx - row * kD;
         float m = kNegBig;
@@ -340,7 +415,7 @@ fa_decode_sm100(const DecodeParams p) {
             acc = fmaf(all_o[(w * kRows + row) * kD + d], f, acc);
             l = fmaf(all_ml[(w * kRows + row) * 2 + 1], f, l);
         }
-        if (p.nsplit == 1) {
+        if (final) {
             if (d < D) {
                 const float inv = l > 0.f ? __frcp_rn(l) : 0.f;
                 store_out<kBf16>(p.o, b * p.o_sb + (static_cast<int64_t>(kvh) * G + row) * p.o_sh + d, acc * inv);
@@ -353,77 +428,77 @@ fa_decode_sm100(const DecodeParams p) {
             }
         }
     }
-    if (p.nsplit == 1) return;
+}
 
-    // ---- last CTA of the unit merges the splits ----
+// After write_range(final = false): count this CTA in on `counter`; the last of the unit's `n`
+// pieces to arrive merges them (piece i lives in workspace slot slot_of(i)), writes O of unit
+// (b, kvh) and re-arms the counter.  Uses the (idle) ring as scratch; block-uniform; every thread
+// must call it.  Returns with the shared memory free again.
+template <int kD, bool kBf16, typename SlotOf>
+__device__ __forceinline__ void arrive_and_merge(const DecodeParams& p, uint8_t* smem, int b, int kvh,
+                                                 int* counter, int n, SlotOf slot_of) {
+    using L = Smem<kD>;
+    using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
+    const int G = p.group, D = p.headdim;
     int* flag = reinterpret_cast<int*>(smem + L::kFlag);
     __threadfence();
     __syncthreads();
-    if (threadIdx.x == 0) *flag = (atomicAdd(p.counters + unit, 1) == p.nsplit - 1);
+    if (threadIdx.x == 0) *flag = (atomicAdd(counter, 1) == n - 1);
     __syncthreads();
     const bool last = *flag != 0;
     __syncthreads();  // the merge below reuses the shared memory the flag lives in
     if (!last) return;
     __threadfence();
     // Every load below is independent of the previous one (the partials come from L2 at some
-    // 600 ns a round trip: a serial loop over the splits would cost more than the whole K/V stream).
-    // 1. all (m, l) pairs of the unit -> shared memory, coalesced float4 loads
-    const int64_t ubase = static_cast<int64_t>(unit) * p.nsplit * kRows;
-    float* sm_ml = reinterpret_cast<float*>(smem);  // [nsplit][kRows][2], later (f, -) in place
+    // 600 ns a round trip: a serial loop over the pieces would cost more than the whole K/V stream).
+    // 1. all (m, l) pairs of the unit -> shared memory, float4 loads (a slot's 32 floats are contiguous)
+    float* sm_ml = reinterpret_cast<float*>(smem);  // [n][kRows][2], later (f, -) in place
     {
-        const float4* src = reinterpret_cast<const float4*>(p.part_ml + ubase * 2);
-        const int n4 = p.nsplit * kRows * 2 / 4;
+        constexpr int kPer = kRows * 2 / 4;  // float4s per slot
+        const int n4 = n * kPer;
 #pragma unroll 4
-        for (int i = threadIdx.x; i < n4; i += kThreads)
-            reinterpret_cast<float4*>(sm_ml)[i] = __ldcg(src + i);
+        for (int i = threadIdx.x; i < n4; i += kThreads) {
+            const int sp = i / kPer, j = i - sp * kPer;
+            reinterpret_cast<float4*>(sm_ml)[i] =
+                __ldcg(reinterpret_cast<const float4*>(p.part_ml + slot_of(sp) * (kRows * 2)) + j);
+        }
     }
     __syncthreads();
-    // 2. per row: global max, total sum, and the weight of every split (8 lanes per row)
+    // 2. per row: global max, total sum, and the weight of every piece (8 lanes per row)
     {
         const int row = threadIdx.x >> 3, part = threadIdx.x & 7;
         float m = kNegBig;
-        for (int sp = part; sp < p.nsplit; sp += 8) m = fmaxf(m, sm_ml[(sp * kRows + row) * 2]);
+        for (int sp = part; sp < n; sp += 8) m = fmaxf(m, sm_ml[(sp * kRows + row) * 2]);
         m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
         m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
         m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 4));
         float l = 0.f;
-        for (int sp = part; sp < p.nsplit; sp += 8)
+        for (int sp = part; sp < n; sp += 8)
             l = fmaf(sm_ml[(sp * kRows + row) * 2 + 1], fast_exp2(sm_ml[(sp * kRows + row) * 2] - m), l);
         l += __shfl_xor_sync(0xffffffffu, l, 1);
         l += __shfl_xor_sync(0xffffffffu, l, 2);
         l += __shfl_xor_sync(0xffffffffu, l, 4);
         const float inv = l > 0.f ? __frcp_rn(l) : 0.f;
-        for (int sp = part; sp < p.nsplit; sp += 8)
+        for (int sp = part; sp < n; sp += 8)
             sm_ml[(sp * kRows + row) * 2] = fast_exp2(sm_ml[(sp * kRows + row) * 2] - m) * inv;
     }
     __syncthreads();
-    // 3. O[row][d..d+3] = sum over splits of weight * partial O, float4 per thread, 8 loads in flight
+    // 3. O[row][d..d+3] = sum over pieces of weight * partial O, float4 per thread, 8 loads in flight
     for (int idx = threadIdx.x; idx < G * (kD / 4); idx += kThreads) {
         const int row = idx / (kD / 4), d = (idx - row * (kD / 4)) * 4;
         if (d >= D) continue;
-        const float4* src = reinterpret_cast<const float4*>(p.part_o + (ubase + row) * kD + d);
-        const int64_t step = static_cast<int64_t>(kRows) * kD / 4;  // float4s between splits
+        const int64_t in_slot = static_cast<int64_t>(row) * kD + d;
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-        int sp = 0;
-        for (; sp + 8 <= p.nsplit; sp += 8) {
-            float4 x[8];
-#pragma unroll
-            for (int u = 0; u < 8; ++u) x[u] = __ldcg(src + (sp + u) * step);
-#pragma unroll
-            for (int u = 0; u < 8; ++u) {
-                const float f = sm_ml[((sp + u) * kRows + row) * 2];
-                acc.x = fmaf(x[u].x, f, acc.x); acc.y = fmaf(x[u].y, f, acc.y);
-                acc.z = fmaf(x[u].z, f, acc.z); acc.w = fmaf(x[u].w, f, acc.w);
-            }
-        }
-        {
+        for (int sp = 0; sp < n; sp += 8) {
             float4 x[8];
 #pragma unroll
             for (int u = 0; u < 8; ++u)
-                x[u] = sp + u < p.nsplit ? __ldcg(src + (sp + u) * step) : make_float4(0.f, 0.f, 0.f, 0.f);
+                x[u] = sp + u < n ? __ldcg(reinterpret_cast<const float4*>(
+                                        p.part_o + slot_of(sp + u) * (kRows * kD) + in_slot))
+                                  : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
             for (int u = 0; u < 8; ++u) {
-                const float f = sp + u < p.nsplit ? sm_ml[((sp + u) * kRows + row) * 2] : 0.f;
+                const float f = sp + u < n ? sm_ml[((sp + u) * kRows + row) * 2] : 0.f;
                 acc.x = fmaf(x[u].x, f, acc.x); acc.y = fmaf(x[u].y, f, acc.y);
                 acc.z = fmaf(x[u].z, f, acc.z); acc.w = fmaf(x[u].w, f, acc.w);
             }
@@ -434,7 +509,442 @@ fa_decode_sm100(const DecodeParams p) {
         packed.y = pack2<kBf16>(acc.z, acc.w);
         *reinterpret_cast<uint2*>(reinterpret_cast<T*>(p.o) + o_idx) = packed;  // D % 8 == 0, 16 B-aligned rows
     }
-    if (threadIdx.x == 0) p.counters[unit] = 0;  // re-arm for the next launch on this workspace
+    if (threadIdx.x == 0) *counter = 0;  // re-arm for the next launch on this slot
+    __syncthreads();
+}
+
+// ---- one CTA per (unit, split): contiguous K/V, or paged K/V beyond kFlatMaxBatch sequences ------
+template <int kD, bool kBf16, bool kPaged>
+__global__ void __launch_bounds__(kThreads, 2)
+fa_decode_sm100(const DecodeParams p) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int unit = blockIdx.x / p.nsplit, split = blockIdx.x - unit * p.nsplit;
+    const int b = unit / p.heads_kv, kvh = unit - b * p.heads_kv;
+    const int key_begin = split * p.chunk;
+    const int seqlen = kPaged ? p.seqlens[b] : p.seqlen_k;
+    const int key_end = min(seqlen, key_begin + p.chunk);
+
+    attend_range<kD, kBf16, kPaged>(p, smem, b, kvh, key_begin, key_end);
+    const int64_t ubase = static_cast<int64_t>(unit) * p.nsplit;
+    write_range<kD, kBf16>(p, smem, b, kvh, p.nsplit == 1, ubase + split);
+    if (p.nsplit == 1) return;
+    arrive_and_merge<kD, kBf16>(p, smem, b, kvh, p.counters + unit, p.nsplit,
+                                [ubase](int i) { return ubase + i; });
+}
+
+
+// ---- paged K/V, the CTAs share the flattened key space -------------------------------------------
+// Unit u = (b, kvh) owns n(b) = max(1, ceil(len(b) / 64)) blocks of the line, units in (b, kvh)
+// order: offset(u) = Hkv · pre[b] + kvh · n(b) with pre the exclusive prefix sum of n.  CTA c takes
+// blocks [c·W, (c+1)·W), W = max(flat_min_blocks, ceil(total / gridDim.x)).  Its range is a run of
+// segments, one per unit it touches; only the first and the last can be partial, so a CTA owns two
+// workspace slots (2c: first segment, 2c + 1: any later one).  A unit cut into pieces spans the
+// CTAs c0 .. c1 and is the LAST segment of c0, so counters[c0] is its own; piece i of it sits in
+// slot 2(c0 + i) for i > 0 and in 2·c0 or 2·c0 + 1 for i = 0 (the former iff the unit starts
+// exactly at c0's range).
+//
+// A block is 64 keys = one 16-key tile for each of the four warps, so all warps change segment at
+// the same block index and the copy pipeline never drains inside a CTA: the tiles of blocks i + 1
+// and i + 2 — of the next unit, if block i ends a segment — are in flight while block i is computed
+// and while the four warps merge, through the ring stage block i just vacated.
+template <int kD>
+struct FlatSmem {
+    using L = Smem<kD>;
+    static constexpr int kPre = L::kRingBytes;                       // int [kFlatMaxBatch + 1]
+    static constexpr int kWarpTotals = kPre + (kFlatMaxBatch + 4) * 4;  // int [kWarps]
+    static constexpr int kML = kWarpTotals + kWarps * 4;             // float [kWarps][kRows][2]
+    static constexpr int kRowScale = kML + kWarps * kRows * 2 * 4;   // float [kRows][2]: (max, 1 / sum)
+    static constexpr int kFlag = kRowScale + kRows * 2 * 4;          // int
+    static constexpr int kTotal = kFlag + 16;
+    static_assert(kRows * kD * 4 <= L::kStageBytes, "a warp's O must fit in one ring stage");
+    static_assert(kML % 16 == 0, "alignment");
+};
+
+struct FlatCursor {
+    int b, kvh, blk;  // block `blk` of unit (b, kvh)
+    int n, len;       // blocks and keys of sequence b
+};
+
+template <int kD, bool kBf16>
+__global__ void __launch_bounds__(kThreads, 2)
+fa_decode_flat_sm100(const DecodeParams p) {
+    using L = Smem<kD>;
+    using F = FlatSmem<kD>;
+    using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
+    constexpr int kKSteps = kD / 16;
+    constexpr int kNBlocks = kD / 8;
+    extern __shared__ __align__(128) uint8_t smem[];
+    int* pre = reinterpret_cast<int*>(smem + F::kPre);
+    const int B = p.batch, Hkv = p.heads_kv, G = p.group, D = p.headdim;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    // ---- exclusive prefix sum of the block counts: thread i owns a run of `per` sequences ----
+    {
+        const int per = (B + kThreads - 1) / kThreads;
+        const int first = threadIdx.x * per, last = min(B, first + per);
+        int sum = 0;
+        for (int i = first; i < last; ++i) sum += max(1, (__ldg(p.seqlens + i) + kFlatBlock - 1) / kFlatBlock);
+        int incl = sum;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int y = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += y;
+        }
+        int* wtot = reinterpret_cast<int*>(smem + F::kWarpTotals);
+        if (lane == 31) wtot[warp] = incl;
+        __syncthreads();
+        int base = incl - sum;
+        for (int w = 0; w < warp; ++w) base += wtot[w];
+        for (int i = first; i < last; ++i) {
+            pre[i] = base;
+            base += max(1, (__ldg(p.seqlens + i) + kFlatBlock - 1) / kFlatBlock);
+        }
+        if (threadIdx.x == kThreads - 1) pre[B] = base;  // the last thread's run ends the line (or is empty)
+        __syncthreads();
+    }
+    const int total = Hkv * pre[B];
+    const int W = max(p.flat_min_blocks, (total + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x));
+    const int cta = blockIdx.x;
+    const int start = cta * W;
+    if (start >= total) return;
+    const int nblk = min(total, start + W) - start;
+
+    // ---- the unit `start` falls into: largest b with Hkv · pre[b] <= start ----
+    FlatCursor cc;
+    {
+        int lo = 0, hi = B;  // invariant: Hkv · pre[lo] <= start < Hkv · pre[hi]
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (Hkv * pre[mid] <= start) lo = mid; else hi = mid;
+        }
+        cc.b = lo;
+        cc.n = pre[lo + 1] - pre[lo];
+        cc.kvh = (start - Hkv * pre[lo]) / cc.n;
+        cc.blk = start - Hkv * pre[lo] - cc.kvh * cc.n;
+        cc.len = __ldg(p.seqlens + lo);
+    }
+    FlatCursor ic = cc;  // the copies run two blocks ahead of the math
+    auto advance = [&](FlatCursor& c) {
+        if (++c.blk < c.n) return;
+        c.blk = 0;
+        if (++c.kvh < Hkv) return;
+        c.kvh = 0;
+        if (++c.b < B) {
+            c.n = pre[c.b + 1] - pre[c.b];
+            c.len = __ldg(p.seqlens + c.b);
+        } else {
+            c.n = 1;  // past the line: never issued, never computed
+            c.len = 0;
+        }
+    };
+    // This warp's tile of a block starts at key blk·64 + warp·16; it never straddles a page.
+    auto table_entry = [&](const FlatCursor& c) {
+        const int key0 = c.blk * kFlatBlock + warp * kTileKeys;
+        const int pg = p.page_shift >= 0 ? key0 >> p.page_shift : key0 / p.page_size;
+        return key0 < c.len ? __ldg(p.block_table + c.b * p.bt_stride + pg) : 0;
+    };
+
+
+    // ---- per-warp cp.async ring, continuous over the CTA's whole range ----
+    const uint32_t ring = smem_addr(smem) + warp * L::kWarpBytes;
+    const T* kpool = reinterpret_cast<const T*>(p.k);
+    const T* vpool = reinterpret_cast<const T*>(p.v);
+    TileCopy<kD> tc;
+    tc.init(p, lane);
+    int phys = table_entry(ic);  // page of the tile the next issue copies
+    int issued = 0, istage = 0;
+    // Copies of block `issued` (at ic).  kSameUnit: the caller knows that the block after it is
+    // in the same unit and inside the CTA's range, which is all the cursor logic there is to skip.
+    auto issue_block = [&](auto same_unit) {
+        constexpr bool kSameUnit = decltype(same_unit)::value;
+        if (kSameUnit || issued < nblk) {
+            const int key0 = ic.blk * kFlatBlock + warp * kTileKeys;
+            if (key0 < ic.len) {
+                const int row0 = p.page_shift >= 0 ? key0 & (p.page_size - 1) : key0 % p.page_size;
+                tc.copy(ring + istage * L::kStageBytes,
+                        kpool + static_cast<int64_t>(phys) * p.k_sp + ic.kvh * p.k_sh + static_cast<int64_t>(row0) * p.k_ss,
+                        vpool + static_cast<int64_t>(phys) * p.v_sp + ic.kvh * p.v_sh + static_cast<int64_t>(row0) * p.v_ss,
+                        ic.len - key0, D, kpool);
+            }
+            ++issued;
+            istage = istage == kStages - 1 ? 0 : istage + 1;
+            if constexpr (kSameUnit) {
+                ++ic.blk;
+                phys = table_entry(ic);  // one issue ahead: its latency is off the path
+            } else {
+                advance(ic);
+                if (issued < nblk) {
+                    phys = table_entry(ic);
+                    if (ic.blk == 0 && lane < G * 2) {  // a new unit two blocks ahead: its q rows -> L2
+                        const T* qrow = reinterpret_cast<const T*>(p.q) + ic.b * p.q_sb +
+                                        (static_cast<int64_t>(ic.kvh) * G + (lane >> 1)) * p.q_sh + (lane & 1) * 64;
+                        if ((lane & 1) * 64 < D) asm volatile("prefetch.global.L2 [%0];" ::"l"(qrow));
+                    }
+                }
+            }
+        }
+        cp_async_commit();  // always commit: the waits count groups
+    };
+    issue_block(std::false_type{});
+    issue_block(std::false_type{});
+
+    float o[kNBlocks][4];
+    float m0, m1, l0, l1;
+    uint32_t qa[kKSteps][4];
+    int cstage = 0;
+    float* ml_all = reinterpret_cast<float*>(smem + F::kML);
+
+    // The warp's tile of block cc.blk: S = Q·Kᵀ, online softmax, O += P·V.  kFull: all 16 keys
+    // exist (every block but the last of a unit).
+    auto compute_block = [&](auto full) {
+        constexpr bool kFull = decltype(full)::value;
+        const uint32_t ks_addr = ring + cstage * L::kStageBytes;
+        const uint32_t vs_addr = ks_addr + L::kTileBytes;
+        const int key0 = cc.blk * kFlatBlock + warp * kTileKeys;
+        if (kFull || key0 < cc.len) {
+            float s[2][4];
+#pragma unroll
+            for (int j = 0; j < 2; ++j) s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
+            {
+                const int krow = ((lane >> 4) << 3) + (lane & 7);  // key row this lane addresses
+                const int khalf = (lane >> 3) & 1;                 // d-low / d-high 8x8 matrix
+#pragma unroll
+                for (int ks = 0; ks < kKSteps; ++ks) {
+                    uint32_t b0, b1, b2, b3;
+                    const int c = 2 * ks + khalf;
+                    ldmatrix_x4(ks_addr + krow * L::kRowBytes + ((c ^ (krow & 7)) << 4), b0, b1, b2, b3);
+                    mma_16816<kBf16>(s[0], qa[ks], b0, b1);
+                    mma_16816<kBf16>(s[1], qa[ks], b2, b3);
+                }
+            }
+            if (!kFull && key0 + kTileKeys > cc.len) {  // keys past the end of the sequence
+#pragma unroll
+                for (int j = 0; j < 2; ++j)
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int key = key0 + j * 8 + (lane & 3) * 2 + (u & 1);
+                        if (key >= cc.len) s[j][u] = -INFINITY;
+                    }
+            }
+            // online softmax, exp2 domain
+            float mx0 = fmaxf(fmaxf(s[0][0], s[0][1]), fmaxf(s[1][0], s[1][1]));
+            float mx1 = fmaxf(fmaxf(s[0][2], s[0][3]), fmaxf(s[1][2], s[1][3]));
+            mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+            mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+            mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+            mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+            const float mn0 = fmaxf(m0, mx0 * p.scale_log2), mn1 = fmaxf(m1, mx1 * p.scale_log2);
+            const float a0 = fast_exp2(m0 - mn0), a1 = fast_exp2(m1 - mn1);
+            m0 = mn0; m1 = mn1;
+            float pr[2][4];
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                pr[j][0] = fast_exp2(fmaf(s[j][0], p.scale_log2, -mn0));
+                pr[j][1] = fast_exp2(fmaf(s[j][1], p.scale_log2, -mn0));
+                pr[j][2] = fast_exp2(fmaf(s[j][2], p.scale_log2, -mn1));
+                pr[j][3] = fast_exp2(fmaf(s[j][3], p.scale_log2, -mn1));
+            }
+            l0 = fmaf(l0, a0, (pr[0][0] + pr[0][1]) + (pr[1][0] + pr[1][1]));
+            l1 = fmaf(l1, a1, (pr[0][2] + pr[0][3]) + (pr[1][2] + pr[1][3]));
+            if (__any_sync(0xffffffffu, a0 != 1.f || a1 != 1.f)) {
+#pragma unroll
+                for (int j = 0; j < kNBlocks; ++j) { o[j][0] *= a0; o[j][1] *= a0; o[j][2] *= a1; o[j][3] *= a1; }
+            }
+            uint32_t pa[4];
+            pa[0] = pack2<kBf16>(pr[0][0], pr[0][1]);
+            pa[1] = pack2<kBf16>(pr[0][2], pr[0][3]);
+            pa[2] = pack2<kBf16>(pr[1][0], pr[1][1]);
+            pa[3] = pack2<kBf16>(pr[1][2], pr[1][3]);
+            {
+                const int vrow = (((lane >> 3) & 1) << 3) + (lane & 7);  // key row
+                const int vsel = lane >> 4;                              // which of the two d-chunks
+#pragma unroll
+                for (int jj = 0; jj < kNBlocks / 2; ++jj) {
+                    uint32_t b0, b1, b2, b3;
+                    const int c = 2 * jj + vsel;
+                    ldmatrix_x4_trans(vs_addr + vrow * L::kRowBytes + ((c ^ (vrow & 7)) << 4), b0, b1, b2, b3);
+                    mma_16816<kBf16>(o[2 * jj], pa, b0, b1);
+                    mma_16816<kBf16>(o[2 * jj + 1], pa, b2, b3);
+                }
+            }
+        }
+        __syncwarp();  // the stage is free: the next issue (or the merge) overwrites it
+        cstage = cstage == kStages - 1 ? 0 : cstage + 1;
+    };
+
+    // q fragments of unit (b, kvh): rows = the G heads of the group, straight from global
+    auto load_q = [&](int b, int kvh) {
+        const T* qbase = reinterpret_cast<const T*>(p.q) + b * p.q_sb + static_cast<int64_t>(kvh) * G * p.q_sh;
+        const int r0 = lane >> 2, c0 = (lane & 3) * 2;
+#pragma unroll
+        for (int ks = 0; ks < kKSteps; ++ks) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int row = r0 + (u & 1) * 8, col = ks * 16 + c0 + (u >> 1) * 8;
+                uint32_t x = 0;
+                if (row < G && col < D) x = __ldg(reinterpret_cast<const uint32_t*>(qbase + row * p.q_sh + col));
+                qa[ks][u] = x;
+            }
+        }
+    };
+    load_q(cc.b, cc.kvh);  // goes out before the first wait: one latency, not two
+
+    for (int i = 0; i < nblk;) {
+        // ---- one segment: blocks cc.blk .. of unit (cc.b, cc.kvh), as far as the range goes ----
+        const int seg_blk0 = cc.blk;
+        const int seg_end = i + min(nblk - i, cc.n - cc.blk);
+        const bool first_segment = i == 0;
+        const bool unit_ends = seg_end - i == cc.n - cc.blk;
+#pragma unroll
+        for (int j = 0; j < kNBlocks; ++j) o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f;
+        m0 = m1 = kNegBig;
+        l0 = l1 = 0.f;
+        // lean part: blocks i + 2 and i + 3 are in this segment, block i is not the unit's last
+        for (; i + 3 < seg_end; ++i) {
+            issue_block(std::true_type{});  // block i + 2, into the stage block i - 1 vacated
+            cp_async_wait<2>();             // blocks i .. i + 2 are pending: i has landed
+            __syncwarp();
+            compute_block(std::true_type{});
+            ++cc.blk;
+        }
+        // the segment's last three blocks: the copies may run into the next unit
+        for (; i < seg_end; ++i) {
+            issue_block(std::false_type{});
+            cp_async_wait<2>();
+            __syncwarp();
+            compute_block(std::false_type{});
+            ++cc.blk;
+        }
+        --cc.blk;  // the segment's last block
+        const FlatCursor done = cc;
+        advance(cc);
+        // q of the next segment: its registers are free now, and the loads fly during the merge
+        if (i < nblk) load_q(cc.b, cc.kvh);
+
+        // ---- merge the four warps through the stage just vacated ----
+        const int mstage = cstage == 0 ? kStages - 1 : cstage - 1;
+        l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+        l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+        l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+        l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+        {
+            float* mo = reinterpret_cast<float*>(smem + warp * L::kWarpBytes + mstage * L::kStageBytes);
+            float* mml = ml_all + warp * kRows * 2;
+            const int r0 = lane >> 2, c0 = (lane & 3) * 2;
+#pragma unroll
+            for (int j = 0; j < kNBlocks; ++j) {
+                *reinterpret_cast<float2*>(mo + r0 * kD + j * 8 + c0) = make_float2(o[j][0], o[j][1]);
+                *reinterpret_cast<float2*>(mo + (r0 + 8) * kD + j * 8 + c0) = make_float2(o[j][2], o[j][3]);
+            }
+            if ((lane & 3) == 0) {
+                mml[r0 * 2] = m0; mml[r0 * 2 + 1] = l0;
+                mml[(r0 + 8) * 2] = m1; mml[(r0 + 8) * 2 + 1] = l1;
+            }
+        }
+        __syncthreads();
+        const bool whole = seg_blk0 == 0 && unit_ends;
+        const int64_t slot = 2 * cta + (first_segment ? 0 : 1);
+        const int64_t o_row0 = done.b * p.o_sb + static_cast<int64_t>(done.kvh) * G * p.o_sh;
+        for (int idx = threadIdx.x; idx < G * kD; idx += kThreads) {
+            const int row = idx / kD, d = idx - row * kD;
+            float m = kNegBig;
+#pragma unroll
+            for (int w = 0; w < kWarps; ++w) m = fmaxf(m, ml_all[(w * kRows + row) * 2]);
+            float acc = 0.f, l = 0.f;
+#pragma unroll
+            for (int w = 0; w < kWarps; ++w) {
+                const float f = fast_exp2(ml_all[(w * kRows + row) * 2] - m);
+                const float* wo = reinterpret_cast<const float*>(smem + w * L::kWarpBytes + mstage * L::kStageBytes);
+                acc = fmaf(wo[row * kD + d], f, acc);
+                l = fmaf(ml_all[(w * kRows + row) * 2 + 1], f, l);
+            }
+            if (whole) {
+                if (d < D) store_out<kBf16>(p.o, o_row0 + row * p.o_sh + d, acc * (l > 0.f ? __frcp_rn(l) : 0.f));
+            } else {
+                p.part_o[(slot * kRows + row) * kD + d] = acc;
+                if (d == 0) {
+                    p.part_ml[(slot * kRows + row) * 2] = m;
+                    p.part_ml[(slot * kRows + row) * 2 + 1] = l;
+                }
+            }
+        }
+        if (!whole) {
+            // ---- one piece of a unit that spans several CTAs: the last to arrive merges ----
+            const int off = start + i - 1 - done.blk;  // offset(u) on the line (block i - 1 was the segment's last)
+            const int c0 = off / W, npieces = (off + done.n - 1) / W - c0 + 1;
+            const int slot0 = 2 * c0 + (off == c0 * W ? 0 : 1);
+            int* flag = reinterpret_cast<int*>(smem + F::kFlag);
+            // Release by ONE thread after the barrier (the fence is cumulative over what the
+            // barrier made visible to it): a fence in every thread would also wait for every
+            // thread's copies in flight, i.e. drain the pipeline this kernel keeps full.
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                __threadfence();
+                *flag = (atomicAdd(p.counters + c0, 1) == npieces - 1);
+            }
+            __syncthreads();
+            if (*flag != 0) {
+                __threadfence();
+                auto slot_of = [c0, slot0](int k) { return static_cast<int64_t>(k == 0 ? slot0 : 2 * (c0 + k)); };
+                // 1. per row: max and 1 / sum over the pieces (8 lanes a row, (m, l) from L2)
+                float* rowscale = reinterpret_cast<float*>(smem + F::kRowScale);
+                {
+                    const int row = threadIdx.x >> 3, part = threadIdx.x & 7;
+                    float m = kNegBig, l = 0.f;
+                    for (int sp = part; sp < npieces; sp += 8) {
+                        const float2 ml = __ldcg(reinterpret_cast<const float2*>(p.part_ml + (slot_of(sp) * kRows + row) * 2));
+                        const float mn = fmaxf(m, ml.x);
+                        l = fmaf(l, fast_exp2(m - mn), ml.y * fast_exp2(ml.x - mn));
+                        m = mn;
+                    }
+#pragma unroll
+                    for (int d = 1; d < 8; d <<= 1) {
+                        const float mo = __shfl_xor_sync(0xffffffffu, m, d), lo = __shfl_xor_sync(0xffffffffu, l, d);
+                        const float mn = fmaxf(m, mo);
+                        l = l * fast_exp2(m - mn) + lo * fast_exp2(mo - mn);
+                        m = mn;
+                    }
+                    if (part == 0) {
+                        rowscale[row * 2] = m;
+                        rowscale[row * 2 + 1] = l > 0.f ? __frcp_rn(l) : 0.f;
+                    }
+                }
+                __syncthreads();
+                // 2. O[row][d..d+3] = sum over pieces of weight · partial O; 8 independent loads in flight
+                for (int idx = threadIdx.x; idx < G * (kD / 4); idx += kThreads) {
+                    const int row = idx / (kD / 4), d = (idx - row * (kD / 4)) * 4;
+                    if (d >= D) continue;
+                    const float rm = rowscale[row * 2], rinv = rowscale[row * 2 + 1];
+                    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+                    for (int sp = 0; sp < npieces; sp += 8) {
+                        float4 x[8];
+                        float pm[8];
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) {
+                            const bool ok = sp + u < npieces;
+                            const int64_t sl = ok ? slot_of(sp + u) : 0;
+                            x[u] = ok ? __ldcg(reinterpret_cast<const float4*>(p.part_o + (sl * kRows + row) * kD + d))
+                                      : make_float4(0.f, 0.f, 0.f, 0.f);
+                            pm[u] = ok ? __ldcg(p.part_ml + (sl * kRows + row) * 2) : kNegBig;
+                        }
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) {
+                            const float f = sp + u < npieces ? fast_exp2(pm[u] - rm) * rinv : 0.f;
+                            acc.x = fmaf(x[u].x, f, acc.x); acc.y = fmaf(x[u].y, f, acc.y);
+                            acc.z = fmaf(x[u].z, f, acc.z); acc.w = fmaf(x[u].w, f, acc.w);
+                        }
+                    }
+                    uint2 packed;
+                    packed.x = pack2<kBf16>(acc.x, acc.y);
+                    packed.y = pack2<kBf16>(acc.z, acc.w);
+                    *reinterpret_cast<uint2*>(reinterpret_cast<T*>(p.o) + o_row0 + row * p.o_sh + d) = packed;
+                }
+                if (threadIdx.x == 0) p.counters[c0] = 0;  // re-arm for the next launch on this slot
+            }
+        }
+        __syncthreads();  // the merge stage and the flag are free again
+    }
+    cp_async_wait<0>();
 }
 
 }  // namespace decode

@@ -65,6 +65,8 @@ constexpr int kMaxDevices = 64;
 constexpr int kSchedSlots = 256;        // launches that may be in flight at once on one device
 constexpr int kDecodeSlots = 64;        // same, split-KV decode launches
 constexpr int kDecodeSlotInts = 512;    // arrival counters of one decode launch (units with nsplit > 1 <= 2 x SMs)
+constexpr int kFlatMinBlocks = 4;       // flattened paged decode: a CTA takes at least 256 keys
+constexpr int kFlatMaxCtas = 384;      // pieces of one unit whose (m, l) fit in the D=64 ring (128 B each), <= kDecodeSlotInts
 struct DeviceState {
     std::once_flag once;
     int error = 0;
@@ -602,6 +604,7 @@ namespace {
 struct DecodePlan {
     int kd, group, units, nsplit, chunk;
     int64_t ml_bytes, o_bytes;
+    int flat_ctas = 0;  // > 0: the CTAs share the flattened key space (paged KV), nsplit == 0
 };
 
 // One wave: two CTAs per SM.  A split shorter than 256 keys is not worth its merge.
@@ -677,7 +680,23 @@ int paged_plan(const fa_sm100_paged_decode_params* p, int num_sms, DecodePlan* d
             return fail(FA_SM100_ERR_INVALID_ARGUMENT,
                         "batch/head strides must be positive multiples of 8 elements (16 bytes)");
     }
-    split_plan(p->max_seqlen_k, int(p->batch * p->heads_kv), p->headdim <= 64 ? 64 : 128, num_sms, dp);
+    const int kd = p->headdim <= 64 ? 64 : 128;
+    const bool flat = p->batch <= fa100::decode::kFlatMaxBatch && !(p->flags & FA_SM100_FLAG_PAGED_ONE_WAVE);
+    if (flat) {
+        // The lengths are device data, so the split cannot be sized per sequence here: one wave of
+        // CTAs shares the flattened key space (fa_sm100_decode.cuh: fa_decode_flat_sm100), each
+        // with two partial slots and one arrival counter.
+        dp->kd = kd;
+        dp->units = int(p->batch * p->heads_kv);
+        dp->nsplit = 0;
+        dp->chunk = kFlatMinBlocks * fa100::decode::kFlatBlock;
+        dp->flat_ctas = 2 * (num_sms > 0 ? num_sms : 148);
+        if (dp->flat_ctas > kFlatMaxCtas) dp->flat_ctas = kFlatMaxCtas;
+        dp->ml_bytes = int64_t(2) * dp->flat_ctas * fa100::decode::kRows * 2 * 4;
+        dp->o_bytes = int64_t(2) * dp->flat_ctas * fa100::decode::kRows * kd * 4;
+        return FA_SM100_OK;
+    }
+    split_plan(p->max_seqlen_k, int(p->batch * p->heads_kv), kd, num_sms, dp);
     return FA_SM100_OK;
 }
 
@@ -692,6 +711,16 @@ DecodeVariant* decode_variant() {
     static DecodeVariant v{fa100::decode::fa_decode_sm100<kD, kBf16, kPaged>, fa100::decode::Smem<kD>::kTotal};
     return &v;
 }
+template <int kD, bool kBf16>
+DecodeVariant* decode_flat_variant() {
+    static DecodeVariant v{fa100::decode::fa_decode_flat_sm100<kD, kBf16>,
+                           fa100::decode::FlatSmem<kD>::kTotal};
+    return &v;
+}
+DecodeVariant* pick_decode_flat(int kd, bool bf16) {
+    return kd == 128 ? (bf16 ? decode_flat_variant<128, true>() : decode_flat_variant<128, false>())
+                     : (bf16 ? decode_flat_variant<64, true>() : decode_flat_variant<64, false>());
+}
 template <bool kPaged>
 DecodeVariant* pick_decode(int kd, bool bf16) {
     return kd == 128 ? (bf16 ? decode_variant<128, true, kPaged>() : decode_variant<128, false, kPaged>())
@@ -699,7 +728,7 @@ DecodeVariant* pick_decode(int kd, bool bf16) {
 }
 
 int check_workspace(const DecodePlan& dp, const void* workspace, int64_t workspace_bytes) {
-    if (dp.nsplit <= 1) return FA_SM100_OK;
+    if (dp.nsplit == 1) return FA_SM100_OK;
     const int64_t need = dp.ml_bytes + dp.o_bytes;
     if (!workspace || workspace_bytes < need)
         return fail(FA_SM100_ERR_INVALID_ARGUMENT,
@@ -707,7 +736,7 @@ int check_workspace(const DecodePlan& dp, const void* workspace, int64_t workspa
                     (long long)need, (long long)workspace_bytes);
     if (reinterpret_cast<uintptr_t>(workspace) & 255u)
         return fail(FA_SM100_ERR_INVALID_ARGUMENT, "decode workspace must be 256-byte aligned");
-    if (dp.units > kDecodeSlotInts)  // cannot happen: nsplit > 1 implies units <= 2 x SMs
+    if (dp.nsplit > 1 && dp.units > kDecodeSlotInts)  // cannot happen: nsplit > 1 implies units <= 2 x SMs
         return fail(FA_SM100_ERR_INVALID_ARGUMENT, "decode split with %d units exceeds the counter slot", dp.units);
     return FA_SM100_OK;
 }
@@ -723,15 +752,16 @@ int launch_decode(DecodeVariant* var, fa100::decode::DecodeParams& kp, const Dec
         return fail(FA_SM100_ERR_CUDA, "cudaFuncSetAttribute(decode): %s", cudaGetErrorString(attr_err));
     kp.nsplit = dp.nsplit;
     kp.chunk = dp.chunk;
-    if (dp.nsplit > 1) {
+    kp.flat_min_blocks = kFlatMinBlocks;
+    if (dp.nsplit != 1) {
         uint8_t* ws = static_cast<uint8_t*>(workspace);
         kp.counters = st->decode_counters +
                       kDecodeSlotInts * (g_decode_seq.fetch_add(1, std::memory_order_relaxed) % kDecodeSlots);
         kp.part_ml = reinterpret_cast<float*>(ws);
         kp.part_o = reinterpret_cast<float*>(ws + dp.ml_bytes);
     }
-    var->fn<<<dim3(dp.units * dp.nsplit), dim3(fa100::decode::kThreads), var->smem_bytes,
-              static_cast<cudaStream_t>(stream)>>>(kp);
+    const int grid = dp.flat_ctas > 0 ? dp.flat_ctas : dp.units * dp.nsplit;
+    var->fn<<<dim3(grid), dim3(fa100::decode::kThreads), var->smem_bytes, static_cast<cudaStream_t>(stream)>>>(kp);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(FA_SM100_ERR_CUDA, "decode kernel launch: %s", cudaGetErrorString(e));
     g_launches.fetch_add(1, std::memory_order_relaxed);
@@ -820,9 +850,13 @@ extern "C" int fa_sm100_fwd_decode_paged(const fa_sm100_paged_decode_params* p, 
     kp.seqlens = p->seqlens_k;
     kp.bt_stride = p->block_table_stride;
     kp.page_size = int(p->page_size);
+    kp.page_shift = -1;
+    for (int sh = 4; sh < 31; ++sh)
+        if ((int64_t(1) << sh) == p->page_size) kp.page_shift = sh;
     kp.scale_log2 = p->softmax_scale * 1.4426950408889634f;
-    return launch_decode(pick_decode<true>(dp.kd, p->dtype == FA_SM100_BF16), kp, dp, st, p->device,
-                         workspace, stream);
+    const bool bf16 = p->dtype == FA_SM100_BF16;
+    return launch_decode(dp.flat_ctas > 0 ? pick_decode_flat(dp.kd, bf16) : pick_decode<true>(dp.kd, bf16), kp, dp,
+                         st, p->device, workspace, stream);
 }
 
 // ------------------------------------------------------------------------------------------------

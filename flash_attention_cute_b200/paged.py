@@ -20,10 +20,36 @@ from . import _lib
 _workspaces: dict = {}
 
 
+FLAG_PAGED_ONE_WAVE = 16  # include/fa_sm100.h: FA_SM100_FLAG_PAGED_ONE_WAVE
+_FLAT_BLOCK = 64          # keys per block of the flattened key space (fa_sm100_decode.cuh: kFlatBlock)
+
+
+def prefer_one_wave(seqlens_host, heads_kv: int, num_sms: int = 148) -> bool:
+    """Host-side choice between the two ways fa_sm100_fwd_decode_paged cuts the work, for callers
+    that have the lengths on the host (serving engines do).  The flattened key space gives every
+    CTA total / (2 SMs) blocks whatever the batch looks like; the one-wave split gives the CTAs of
+    the longest sequence max_len / nsplit.  The latter has fewer partial results, which is worth
+    some imbalance: it is chosen while its longest CTA stays within 1.3x the fair share."""
+    lens = [int(n) for n in seqlens_host]
+    if not lens or len(lens) > 2048:
+        return True
+    slots = 2 * num_sms
+    units = len(lens) * heads_kv
+    total = heads_kv * sum(max(1, -(-n // _FLAT_BLOCK)) for n in lens)
+    fair = max(4.0, total / slots)
+    max_len = max(max(lens), 1)
+    nsplit = max(1, min(slots // units if units <= slots else 1, max_len // 256))
+    longest = -(-max_len // nsplit) / _FLAT_BLOCK
+    return longest <= 1.3 * fair
+
+
 def flash_attn_decode_paged(q, k_cache, v_cache, block_table, seqlens_k, softmax_scale=None,
-                            max_seqlen_k=None):
+                            max_seqlen_k=None, seqlens_k_host=None, one_wave=None):
     """q: [B, Hq, D] or [B, Hq, 1, D]; returns o of the same shape.  ``max_seqlen_k`` (an upper
-    bound of seqlens_k known on the host) sizes the split; default: the table's capacity."""
+    bound of seqlens_k known on the host) sizes the split; default: the table's capacity.
+    ``one_wave``: True = split every sequence alike (FA_SM100_FLAG_PAGED_ONE_WAVE), False = the
+    CTAs share the flattened key space (robust against ragged batches), None = decide from
+    ``seqlens_k_host`` (the same lengths as a host list / CPU tensor) when given, else False."""
     if not (q.is_cuda and k_cache.is_cuda and v_cache.is_cuda):
         raise NotImplementedError(
             "flash_attn_decode_paged is implemented for CUDA (sm_100a / B200) tensors only; "
@@ -70,6 +96,10 @@ def flash_attn_decode_paged(q, k_cache, v_cache, block_table, seqlens_k, softmax
     p.softmax_scale = float(D ** -0.5 if softmax_scale is None else softmax_scale)
     p.dtype = _lib.FA_SM100_BF16 if q3.dtype == torch.bfloat16 else _lib.FA_SM100_FP16
     p.device = q3.device.index if q3.device.index is not None else torch.cuda.current_device()
+    if one_wave is None:
+        one_wave = seqlens_k_host is not None and prefer_one_wave(
+            seqlens_k_host.tolist() if hasattr(seqlens_k_host, "tolist") else seqlens_k_host, k_cache.size(2))
+    p.flags = FLAG_PAGED_ONE_WAVE if one_wave else 0
     stream = torch.cuda.current_stream(q3.device).cuda_stream
     nbytes = ctypes.c_int64()
     _lib.raise_for_status(lib.fa_sm100_paged_decode_plan(ctypes.byref(p), None, None, ctypes.byref(nbytes)))

@@ -58,6 +58,9 @@ enum fa_sm100_status {
 #define FA_SM100_FLAG_FORCE_PACK_GQA 2u /* pack whenever Hq/Hkv > 1 (default: heuristic)        */
 #define FA_SM100_FLAG_NO_DECODE 8u      /* operator-level routing hint: keep seqlen_q == 1 on
                                            fa_sm100_fwd instead of fa_sm100_fwd_decode            */
+#define FA_SM100_FLAG_PAGED_ONE_WAVE 16u /* fa_sm100_fwd_decode_paged: the caller knows that the
+                                           sequence lengths are close to max_seqlen_k; split every
+                                           sequence alike instead of sharing the flattened key space */
 /* Tuning bits (honoured by builds with -DFA_SM100_TUNE, ignored by the product build):
  *   bits 8-11  1 + number of exp2 evaluations per 8 element pairs moved to the FMA pipe (0 = default)
  *   bits 12-13 speculative stale-max softmax: 0 = default, 1 = off, 2 = on
@@ -143,9 +146,23 @@ int64_t fa_sm100_static_scratch_bytes(void);
  * (page, kv-head, in-page token, d) = page * kv_strides[0] + head * kv_strides[1] +
  * token * kv_strides[2] + d, which covers both [pages, page_size, Hkv, D] and
  * [pages, Hkv, page_size, D].  page_size must be a multiple of 16.  seqlens_k and block_table are
- * DEVICE int32 arrays (read by the kernel, no host sync); max_seqlen_k only sizes the split and
- * must be >= every seqlens_k[b].  Same split-KV kernel, workspace rules and numerics as
- * fa_sm100_fwd_decode; a sequence with no keys yields zeros. */
+ * DEVICE int32 arrays (read by the kernel, no host sync); max_seqlen_k must be >= every
+ * seqlens_k[b].  A sequence with no keys yields zeros.  Same numerics and workspace rules as
+ * fa_sm100_fwd_decode.
+ *
+ * How the work is cut (the lengths are device data, the host cannot size a split per sequence):
+ *   default — the CTAs of one wave (2 per SM) share the FLATTENED key space: every (sequence,
+ *     kv-head) unit owns ceil(len / 64) blocks of 64 keys laid end to end and each CTA streams an
+ *     equal run of blocks, whichever units they belong to; a unit cut between CTAs is merged by the
+ *     last of them to arrive.  Every CTA reads the same number of bytes however ragged the batch
+ *     is (one 16 K-key sequence among 31 of 512 keys: 4.2x faster than the split below).  Up to
+ *     2048 sequences; the plan reports nsplit = 0 and chunk_keys = the smallest run of a CTA.
+ *   FA_SM100_FLAG_PAGED_ONE_WAVE (or more than 2048 sequences) — every unit is cut into the same
+ *     number of chunks, sized from max_seqlen_k so that one wave covers the GPU, exactly as
+ *     fa_sm100_fwd_decode does.  3-10 % faster when all lengths are close to max_seqlen_k (chunk
+ *     boundaries coincide with unit boundaries: fewer partial results), much slower when a few
+ *     sequences are far longer than the rest (their CTAs finish last, alone).  A caller that has
+ *     the lengths on the host can choose per batch: flash_attention_cute_b200/paged.py does. */
 typedef struct fa_sm100_paged_decode_params {
     const void* q;        /* [B, Hq, D] element strides q_strides = {batch, head} */
     const void* k_cache;

@@ -168,7 +168,7 @@ def test_decode_shape_changes_on_one_stream(cuda_device):
 def _paged_case(B, Hq, Hkv, D, page, lens, dtype, device, seed, layout="pshd", shared=False):
     """Random pages in random order; returns (q, k_cache, v_cache, block_table, seqlens, dense k, dense v)."""
     g = torch.Generator(device=device).manual_seed(seed)
-    max_pages = (max(lens) + page - 1) // page
+    max_pages = max(1, (max(lens) + page - 1) // page)
     n_pages = B * max_pages + 3
     if layout == "pshd":
         kc = torch.randn(n_pages, page, Hkv, D, generator=g, device=device).to(dtype)
@@ -185,6 +185,18 @@ def _paged_case(B, Hq, Hkv, D, page, lens, dtype, device, seed, layout="pshd", s
     dense_k = kc[bt.long()].reshape(B, max_pages * page, Hkv, D).transpose(1, 2)  # [B, Hkv, S, D]
     dense_v = vc[bt.long()].reshape(B, max_pages * page, Hkv, D).transpose(1, 2)
     return q, kc, vc, bt, sl, dense_k, dense_v
+
+
+def test_prefer_one_wave_from_host_lengths():
+    from flash_attention_cute_b200.paged import prefer_one_wave
+
+    assert prefer_one_wave([8192] * 16, 8)                    # uniform, chunks align with units
+    assert prefer_one_wave([4096] * 64, 8)                    # 512 equal units, one CTA each
+    assert not prefer_one_wave([16384] + [512] * 31, 8)       # one long sequence among short ones
+    assert not prefer_one_wave([1024 + 478 * i for i in range(16)], 8)   # 1 K ... 8 K
+    assert prefer_one_wave([64 + 4 * i for i in range(256)], 8)          # 2048 short units
+    assert not prefer_one_wave([131072] + [100] * 255, 8)     # ... unless one of them is huge
+    assert prefer_one_wave([100] * 3000, 8)                   # beyond what the flat kernel takes
 
 
 def test_paged_plan_validation():
@@ -204,7 +216,17 @@ def test_paged_plan_validation():
     p.softmax_scale = 0.088
     ns, ch, nb = ctypes.c_int32(), ctypes.c_int32(), ctypes.c_int64()
     assert lib.fa_sm100_paged_decode_plan(ctypes.byref(p), ctypes.byref(ns), ctypes.byref(ch), ctypes.byref(nb)) == 0
+    # per-sequence lengths are device data: one wave of CTAs (2 per SM) shares the flattened key
+    # space, two partial slots per CTA, at least 256 keys per CTA; nsplit 0 says so
+    assert ns.value == 0 and ch.value == 256 and nb.value == 2 * 296 * 16 * (128 + 2) * 4
+    p.batch = 4096   # more sequences than a CTA keeps prefix sums for: one CTA per (unit, split)
+    assert lib.fa_sm100_paged_decode_plan(ctypes.byref(p), ctypes.byref(ns), ctypes.byref(ch), ctypes.byref(nb)) == 0
+    assert ns.value == 1 and nb.value == 0
+    p.batch = 16
+    p.flags = 16     # FA_SM100_FLAG_PAGED_ONE_WAVE: the split of the contiguous decode kernel
+    assert lib.fa_sm100_paged_decode_plan(ctypes.byref(p), ctypes.byref(ns), ctypes.byref(ch), ctypes.byref(nb)) == 0
     assert ns.value == 2 and ch.value == 4096 and nb.value == 128 * 2 * 16 * (128 + 2) * 4
+    p.flags = 0
     p.page_size = 24
     assert lib.fa_sm100_paged_decode_plan(ctypes.byref(p), None, None, None) == 1
     assert "multiple of 16" in _lib.last_error()
@@ -223,13 +245,14 @@ def test_paged_plan_validation():
     (5, 8, 8, 128, 64, [700, 64, 65, 63, 1024], "pshd", True),      # shared prefix page
     (1, 32, 8, 128, 128, [32768], "pshd", False),                   # one long sequence, many splits
 ])
-def test_paged_decode_matches_oracle(cuda_device, dtype, B, Hq, Hkv, D, page, lens, layout, shared):
+@pytest.mark.parametrize("one_wave", [False, True], ids=["flat", "one_wave"])
+def test_paged_decode_matches_oracle(cuda_device, dtype, B, Hq, Hkv, D, page, lens, layout, shared, one_wave):
     from flash_attention import flash_attn_decode_paged
     from flash_attention_cute_b200 import _lib
 
     q, kc, vc, bt, sl, dk, dv = _paged_case(B, Hq, Hkv, D, page, lens, dtype, cuda_device, 77, layout, shared)
     n0 = _lib.launch_count()
-    out = flash_attn_decode_paged(q, kc, vc, bt, sl, max_seqlen_k=max(max(lens), 1))
+    out = flash_attn_decode_paged(q, kc, vc, bt, sl, max_seqlen_k=max(max(lens), 1), one_wave=one_wave)
     _lib.check_device(0)
     assert _lib.launch_count() == n0 + 1 and out.shape == q.shape
     for b, n in enumerate(lens):
@@ -242,7 +265,69 @@ def test_paged_decode_matches_oracle(cuda_device, dtype, B, Hq, Hkv, D, page, le
     # same keys through the contiguous decode kernel: bit-equal when the split is the same
     if len(set(lens)) == 1 and lens[0] % page == 0:
         dense = _ext().flash_attention_fwd(q.unsqueeze(2), dk.contiguous(), dv.contiguous(), D ** -0.5, False)
-        assert torch.equal(dense[:, :, 0], out)
+        if one_wave:
+            assert torch.equal(dense[:, :, 0], out)
+        else:
+            assert_close(out, dense[:, :, 0].float(), dtype, "paged (flattened) vs contiguous decode")
+
+
+def _check_paged(cuda_device, B, Hq, Hkv, D, page, lens, dtype, seed, sample=None):
+    from flash_attention import flash_attn_decode_paged
+    from flash_attention_cute_b200 import _lib
+
+    q, kc, vc, bt, sl, dk, dv = _paged_case(B, Hq, Hkv, D, page, lens, dtype, cuda_device, seed)
+    n0 = _lib.launch_count()
+    out = flash_attn_decode_paged(q, kc, vc, bt, sl, max_seqlen_k=max(max(lens), 1))
+    _lib.check_device(0)
+    assert _lib.launch_count() == n0 + 1
+    again = flash_attn_decode_paged(q, kc, vc, bt, sl, max_seqlen_k=max(max(lens), 1))
+    assert torch.equal(out, again), "two launches on the same inputs differ (stale counters or partials)"
+    for b in (range(B) if sample is None else sample):
+        n = lens[b]
+        if n == 0:
+            assert not out[b].any()
+            continue
+        ref = eager_attention(q[b:b + 1].unsqueeze(2), dk[b:b + 1, :, :n], dv[b:b + 1, :, :n], None, False,
+                              out_dtype=torch.float32)
+        assert_close(out[b:b + 1].unsqueeze(2), ref, dtype, f"paged seq {b} len {n}")
+    return out
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["many_short", "skewed", "tiny_total", "all_empty", "exact_blocks", "d64_mqa"])
+def test_paged_decode_flattened_key_space(cuda_device, name):
+    """The CTAs share the flattened key space (fa_decode_flat_sm100): ranges that hold many whole
+    units, units cut into 2 .. 40 pieces, a unit that starts exactly at a range boundary, batches
+    whose total is below one range, empty sequences between non-empty ones."""
+    import random
+
+    rng = random.Random(11)
+    if name == "many_short":      # 300 x 2 units, 0 .. 600 keys: a CTA walks several units
+        lens = [rng.choice([0, 1, 63, 64, 65, rng.randrange(1, 600)]) for _ in range(300)]
+        _check_paged(cuda_device, 300, 8, 2, 128, 64, lens, torch.bfloat16, 1, sample=range(0, 300, 7))
+    elif name == "skewed":        # one 16 K sequence cut into many pieces, 31 short ones
+        lens = [16384] + [rng.randrange(1, 700) for _ in range(31)]
+        _check_paged(cuda_device, 32, 64, 8, 128, 128, lens, torch.bfloat16, 2)
+    elif name == "tiny_total":    # fewer blocks than CTAs: most CTAs have nothing to do
+        _check_paged(cuda_device, 2, 8, 1, 128, 16, [100, 30], torch.float16, 3)
+    elif name == "all_empty":
+        out = _check_paged(cuda_device, 5, 16, 4, 128, 16, [0] * 5, torch.float16, 4)
+        assert not out.any()
+    elif name == "exact_blocks":  # 37 units of exactly 8 blocks: W = 4 -> every unit starts a range
+        _check_paged(cuda_device, 37, 4, 1, 128, 64, [512] * 37, torch.bfloat16, 5)
+    else:                          # D = 64, MQA with 14 q heads, ragged
+        lens = [rng.randrange(0, 3000) for _ in range(24)]
+        _check_paged(cuda_device, 24, 14, 1, 64, 32, lens, torch.float16, 6)
+
+
+@pytest.mark.gpu
+def test_paged_decode_more_sequences_than_the_flat_kernel_takes(cuda_device):
+    """B > 2048: one CTA per unit (fa_decode_sm100<paged>), lengths still per sequence."""
+    import random
+
+    rng = random.Random(5)
+    lens = [rng.randrange(0, 80) for _ in range(2100)]
+    _check_paged(cuda_device, 2100, 4, 1, 128, 16, lens, torch.bfloat16, 8, sample=range(0, 2100, 97))
 
 
 @pytest.mark.gpu
