@@ -1021,7 +1021,9 @@ extern "C" int fa_sm100_rope(const fa_sm100_rope_params* p, void* stream) {
     kp.cs_ss = p->cos_sin_strides[1];
     kp.total = total;
     // enough CTAs to keep every SM's load queue full (8 per SM), grid-stride over the rest
-    long long blocks = (long long)p->batch * p->seqlen;  // one (batch, position) row per loop turn
+    const long long row_items = (p->heads_q + p->heads_kv) * (p->headdim / 16);
+    const long long rpp = row_items >= fa100::rope::kThreads ? 1 : fa100::rope::kThreads / row_items;
+    long long blocks = ((long long)p->batch * p->seqlen + rpp - 1) / rpp;  // rpp (batch, position) rows side by side per block
     const long long cap = 8ll * (st->num_sms > 0 ? st->num_sms : 148);
     if (blocks > cap) blocks = cap;
     if (p->dtype == FA_SM100_BF16)

@@ -73,8 +73,16 @@ fa_rope_sm100(const RopeParams p) {
     const unsigned rows = static_cast<unsigned>(p.batch) * p.seqlen;
     constexpr uint32_t kNeg = 0x80008000u;
     constexpr int kRowsPerTurn = 4;  // independent rows per loop turn: 8 data loads in flight per thread
-    for (unsigned row0 = blockIdx.x; row0 < rows; row0 += kRowsPerTurn * gridDim.x) {
-        for (unsigned j = threadIdx.x; j < items; j += kThreads) {
+    // Few heads or a small head dimension (Qwen2-0.5B: 16 heads x 4 chunks = 64 items a row): the
+    // block covers rpp rows side by side instead of leaving three quarters of its threads idle.
+    const unsigned rpp = items >= kThreads ? 1u : kThreads / items;
+    const unsigned sub = rpp > 1 ? threadIdx.x / items : 0u;
+    const unsigned j0 = threadIdx.x - sub * items;
+    const unsigned jstep = rpp > 1 ? items : static_cast<unsigned>(kThreads);
+    const unsigned rstep = gridDim.x * rpp;
+    if (sub >= rpp) return;
+    for (unsigned row0 = blockIdx.x * rpp + sub; row0 < rows; row0 += kRowsPerTurn * rstep) {
+        for (unsigned j = j0; j < items; j += jstep) {
             const unsigned h = j / chunks, c = j - h * chunks;
             const bool is_q = h < static_cast<unsigned>(p.heads_q);
             const unsigned hh = is_q ? h : h - p.heads_q;
@@ -86,7 +94,7 @@ fa_rope_sm100(const RopeParams p) {
             uint16_t* dst[kRowsPerTurn];
 #pragma unroll
             for (int u = 0; u < kRowsPerTurn; ++u) {
-                const unsigned row = row0 + u * gridDim.x;
+                const unsigned row = row0 + u * rstep;
                 dst[u] = nullptr;
                 if (row < rows) {
                     const unsigned b = row / static_cast<unsigned>(p.seqlen), s = row - b * p.seqlen;

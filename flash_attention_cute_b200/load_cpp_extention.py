@@ -70,6 +70,7 @@ class FlashAttentionExtension:
         self._lib = _lib.load()
         self._workspaces = {}
         self._plans = {}  # problem key -> (FwdParams bytes, use_decode, workspace bytes, o strides)
+        self._rope_plans = {}  # problem key -> RopeParams bytes
 
     def flash_attention_fwd(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor,
                             softmax_scale: float, causal: bool, flags: int = 0) -> torch.Tensor:
@@ -161,6 +162,23 @@ class FlashAttentionExtension:
         """(q·cos + rotate_half(q)·sin, k·cos + rotate_half(k)·sin) in one kernel, bit-equal to the
         reference expression (models/rope_attn_fwd.py:14-38).  q [B,Hq,S,D], k [B,Hkv,S,D] (strided
         views welcome), cos / sin [B or 1, S, D].  Outputs keep the inputs' strides."""
+        # Fast path, as in flash_attention_fwd: this exact problem has been validated before, only
+        # the pointers change (the checks and the params fill are ~20 us of Python, more than the
+        # kernel on decode-sized inputs).
+        key = (q.shape, q.stride(), k.shape, k.stride(), cos.shape, cos.stride(), sin.stride(), q.dtype, k.dtype,
+               cos.dtype, sin.dtype, q.device, k.device, cos.device, sin.device)
+        ent = self._rope_plans.get(key)
+        if ent is not None and not ((q.data_ptr() | k.data_ptr() | cos.data_ptr() | sin.data_ptr()) & 15):
+            q_out, k_out = torch.empty_like(q), torch.empty_like(k)
+            if q_out.stride() == q.stride() and k_out.stride() == k.stride() and \
+                    not ((q_out.data_ptr() | k_out.data_ptr()) & 15):
+                p = _lib.RopeParams.from_buffer_copy(ent)
+                p.q, p.k, p.q_out, p.k_out = q.data_ptr(), k.data_ptr(), q_out.data_ptr(), k_out.data_ptr()
+                p.cos, p.sin = cos.data_ptr(), sin.data_ptr()
+                stream = torch.cuda.current_stream(q.device).cuda_stream
+                _lib.raise_for_status(self._lib.fa_sm100_rope(ctypes.byref(p), ctypes.c_void_p(stream)))
+                return q_out, k_out
+        q_in, k_in, cos_in, sin_in = q, k, cos, sin
         _check(q.dim() == 4 and k.dim() == 4, "q, k must be 4-D [batch, heads, seq, dim]")
         _check(cos.dim() == 3 and sin.dim() == 3 and cos.shape == sin.shape, "cos, sin must be 3-D [batch, seq, dim]")
         _check(q.size(0) == k.size(0) and q.size(2) == k.size(2) and q.size(3) == k.size(3),
@@ -197,6 +215,11 @@ class FlashAttentionExtension:
         p.device = q.device.index if q.device.index is not None else torch.cuda.current_device()
         stream = torch.cuda.current_stream(q.device).cuda_stream
         _lib.raise_for_status(self._lib.fa_sm100_rope(ctypes.byref(p), ctypes.c_void_p(stream)))
+        if q is q_in and k is k_in and cos is cos_in and sin is sin_in and q_out.stride() == q.stride() \
+                and k_out.stride() == k.stride():   # nothing was copied: the plan holds for this key
+            if len(self._rope_plans) >= 1024:
+                self._rope_plans.clear()
+            self._rope_plans[key] = bytes(p)
         return q_out, k_out
 
     def decode_plan(self, q, k, v) -> dict:

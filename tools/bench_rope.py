@@ -11,7 +11,11 @@ sys.path.insert(0, str(ROOT))
 from flash_attention_cute_b200.load_cpp_extention import load_extension  # noqa: E402
 from flash_attention_cute_b200.models.rope_attn_fwd import rotate_half  # noqa: E402
 
-SHAPES = {"c3_llama8b_b8_s8k": (8, 32, 8, 8192, 128), "c5_b1_s4k": (1, 32, 8, 4096, 128), "qwen_b4_s2k_d64": (4, 14, 2, 2048, 64)}
+sys.path.insert(0, str(ROOT / "tools"))
+from bench_decode import time_graph  # noqa: E402
+
+SHAPES = {"c3_llama8b_b8_s8k": (8, 32, 8, 8192, 128), "c5_b1_s4k": (1, 32, 8, 4096, 128), "qwen_b4_s2k_d64": (4, 14, 2, 2048, 64),
+          "decode_b16_s1": (16, 32, 8, 1, 128)}
 
 
 def timeit(fn, iters=20, warmup=5):
@@ -47,9 +51,15 @@ def main():
             return (q * c) + (rotate_half(q) * s), (k * c) + (rotate_half(k) * s)
 
         ms_f = timeit(lambda: ext.rope(q, k, cos, sin))
+        # the same calls replayed from one CUDA graph, inputs rotated through > L2: the kernel's own
+        # time, without the host cost of a call (fused_us above includes it when the GPU is idle)
+        ncopies = max(2, min(16, int(3e8 // nbytes) + 1))
+        sets = [(q.clone(), k.clone(), cos, sin) for _ in range(ncopies)]
+        ms_g = time_graph(lambda a_, b_, c_, d_: ext.rope(a_, b_, c_, d_), sets, 50, 5)
         ms_e = timeit(eager)
         a, b = ext.rope(q, k, cos, sin), eager()
         rec = {"shape": name, "B": B, "Hq": Hq, "Hkv": Hkv, "S": S, "D": D, "bytes": nbytes,
+               "graph_us": ms_g * 1e3, "graph_gbs": nbytes / ms_g / 1e6, "graph_frac_hbm": nbytes / ms_g / 1e6 / hbm,
                "fused_us": ms_f * 1e3, "fused_gbs": nbytes / ms_f / 1e6, "frac_hbm": nbytes / ms_f / 1e6 / hbm,
                "eager_us": ms_e * 1e3, "speedup": ms_e / ms_f, "hbm_peak_gbs": hbm,
                "bit_equal": bool(torch.equal(a[0], b[0]) and torch.equal(a[1], b[1]))}
