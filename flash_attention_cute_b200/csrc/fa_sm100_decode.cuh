@@ -36,6 +36,8 @@
 #include <cuda_fp16.h>
 #include <stdint.h>
 
+#include <cooperative_groups.h>
+
 #include <type_traits>
 
 namespace fa100 {
@@ -90,8 +92,11 @@ struct Smem {
     static constexpr int kMergeO = 0;                                // float [kWarps][kRows][kD]
     static constexpr int kMergeML = kWarps * kRows * kD * 4;         // float [kWarps][kRows][2]
     static constexpr int kFlag = kMergeML + kWarps * kRows * 2 * 4;  // int
-    static constexpr int kTotal = kRingBytes > kFlag + 16 ? kRingBytes : kFlag + 16;
-    static_assert(kFlag + 16 <= kRingBytes, "merge buffers must fit in the ring");
+    // cluster merge: this CTA's combined partial, read by rank 0 of the cluster through DSMEM
+    static constexpr int kClusterO = (kFlag + 16 + 255) / 256 * 256;  // float [kRows][kD]
+    static constexpr int kClusterML = kClusterO + kRows * kD * 4;     // float [kRows][2]
+    static constexpr int kTotal = kRingBytes;
+    static_assert(kClusterML + kRows * 2 * 4 <= kRingBytes, "merge buffers must fit in the ring");
 };
 
 __device__ __forceinline__ uint32_t smem_addr(const void* p) {
@@ -394,15 +399,15 @@ __device__ __forceinline__ void attend_range(const DecodeParams& p, uint8_t* sme
 }
 
 // Combine the four warps' triples left by attend_range and either write O of unit (b, kvh)
-// (final: the range was the whole unit) or the partial into workspace slot `slot`.
+// (final: the range was the whole unit) or the partial: O [kRows][kD] to dst_o, (m, l) pairs to
+// dst_ml (a workspace slot, or this CTA's own shared memory for the cluster merge).
 template <int kD, bool kBf16>
 __device__ __forceinline__ void write_range(const DecodeParams& p, const uint8_t* smem, int b, int kvh,
-                                            bool final, int64_t slot) {
+                                            bool final, float* dst_o, float* dst_ml) {
     using L = Smem<kD>;
     const int G = p.group, D = p.headdim;
     const float* all_o = reinterpret_cast<const float*>(smem + L::kMergeO);
     const float* all_ml = reinterpret_cast<const float*>(smem + L::kMergeML);
-    const int64_t part_base = slot * kRows;
     for (int idx = threadIdx.x; idx < G * kD; idx += kThreads) {
         const int row = idx / kD, d = idx - row * kD;
         float m = kNegBig;
@@ -421,46 +426,55 @@ __device__ __forceinline__ void write_range(const DecodeParams& p, const uint8_t
                 store_out<kBf16>(p.o, b * p.o_sb + (static_cast<int64_t>(kvh) * G + row) * p.o_sh + d, acc * inv);
             }
         } else {
-            p.part_o[(part_base + row) * kD + d] = acc;
+            dst_o[row * kD + d] = acc;
             if (d == 0) {
-                p.part_ml[(part_base + row) * 2] = m;
-                p.part_ml[(part_base + row) * 2 + 1] = l;
+                dst_ml[row * 2] = m;
+                dst_ml[row * 2 + 1] = l;
             }
         }
     }
 }
 
-// After write_range(final = false): count this CTA in on `counter`; the last of the unit's `n`
-// pieces to arrive merges them (piece i lives in workspace slot slot_of(i)), writes O of unit
-// (b, kvh) and re-arms the counter.  Uses the (idle) ring as scratch; block-uniform; every thread
-// must call it.  Returns with the shared memory free again.
-template <int kD, bool kBf16, typename SlotOf>
-__device__ __forceinline__ void arrive_and_merge(const DecodeParams& p, uint8_t* smem, int b, int kvh,
-                                                 int* counter, int n, SlotOf slot_of) {
+// After write_range(final = false): count this CTA in on `counter`; true for the last of the
+// unit's `n` pieces to arrive (block-uniform; every thread must call it).
+template <int kD>
+__device__ __forceinline__ bool arrive_last(uint8_t* smem, int* counter, int n) {
     using L = Smem<kD>;
-    using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
-    const int G = p.group, D = p.headdim;
     int* flag = reinterpret_cast<int*>(smem + L::kFlag);
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) *flag = (atomicAdd(counter, 1) == n - 1);
     __syncthreads();
     const bool last = *flag != 0;
-    __syncthreads();  // the merge below reuses the shared memory the flag lives in
-    if (!last) return;
-    __threadfence();
+    __syncthreads();  // the merge reuses the shared memory the flag lives in
+    if (last) __threadfence();
+    return last;
+}
+
+// Merge the `n` pieces of unit (b, kvh) and write its O.  ml_of(i) / o_of(i): the 32 (m, l)
+// floats and the [kRows][kD] partial O of piece i — workspace slots in L2 (kL2: ld.global.cg) or
+// the shared memory of the CTAs of a cluster (plain generic loads).  Uses the first n·128 bytes of
+// the (idle) ring as scratch; every thread of the CTA must call it.
+template <int kD, bool kBf16, bool kL2, typename MlOf, typename OOf>
+__device__ __forceinline__ void merge_pieces(const DecodeParams& p, uint8_t* smem, int b, int kvh, int n,
+                                             MlOf ml_of, OOf o_of) {
+    using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
+    const int G = p.group, D = p.headdim;
+    auto ld4 = [](const float* ptr) {
+        if constexpr (kL2) return __ldcg(reinterpret_cast<const float4*>(ptr));
+        else return *reinterpret_cast<const float4*>(ptr);
+    };
     // Every load below is independent of the previous one (the partials come from L2 at some
     // 600 ns a round trip: a serial loop over the pieces would cost more than the whole K/V stream).
-    // 1. all (m, l) pairs of the unit -> shared memory, float4 loads (a slot's 32 floats are contiguous)
+    // 1. all (m, l) pairs of the unit -> shared memory, float4 loads (a piece's 32 floats are contiguous)
     float* sm_ml = reinterpret_cast<float*>(smem);  // [n][kRows][2], later (f, -) in place
     {
-        constexpr int kPer = kRows * 2 / 4;  // float4s per slot
+        constexpr int kPer = kRows * 2 / 4;  // float4s per piece
         const int n4 = n * kPer;
 #pragma unroll 4
         for (int i = threadIdx.x; i < n4; i += kThreads) {
             const int sp = i / kPer, j = i - sp * kPer;
-            reinterpret_cast<float4*>(sm_ml)[i] =
-                __ldcg(reinterpret_cast<const float4*>(p.part_ml + slot_of(sp) * (kRows * 2)) + j);
+            reinterpret_cast<float4*>(sm_ml)[i] = ld4(ml_of(sp) + j * 4);
         }
     }
     __syncthreads();
@@ -487,15 +501,13 @@ __device__ __forceinline__ void arrive_and_merge(const DecodeParams& p, uint8_t*
     for (int idx = threadIdx.x; idx < G * (kD / 4); idx += kThreads) {
         const int row = idx / (kD / 4), d = (idx - row * (kD / 4)) * 4;
         if (d >= D) continue;
-        const int64_t in_slot = static_cast<int64_t>(row) * kD + d;
+        const int in_piece = row * kD + d;
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
         for (int sp = 0; sp < n; sp += 8) {
             float4 x[8];
 #pragma unroll
             for (int u = 0; u < 8; ++u)
-                x[u] = sp + u < n ? __ldcg(reinterpret_cast<const float4*>(
-                                        p.part_o + slot_of(sp + u) * (kRows * kD) + in_slot))
-                                  : make_float4(0.f, 0.f, 0.f, 0.f);
+                x[u] = sp + u < n ? ld4(o_of(sp + u) + in_piece) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
             for (int u = 0; u < 8; ++u) {
                 const float f = sp + u < n ? sm_ml[((sp + u) * kRows + row) * 2] : 0.f;
@@ -509,14 +521,19 @@ __device__ __forceinline__ void arrive_and_merge(const DecodeParams& p, uint8_t*
         packed.y = pack2<kBf16>(acc.z, acc.w);
         *reinterpret_cast<uint2*>(reinterpret_cast<T*>(p.o) + o_idx) = packed;  // D % 8 == 0, 16 B-aligned rows
     }
-    if (threadIdx.x == 0) *counter = 0;  // re-arm for the next launch on this slot
     __syncthreads();
 }
 
-// ---- one CTA per (unit, split): contiguous K/V, or paged K/V beyond kFlatMaxBatch sequences ------
-template <int kD, bool kBf16, bool kPaged>
+// ---- one CTA per (unit, split): contiguous K/V, or paged K/V with the per-sequence split ---------
+// kCluster: the nsplit (2 .. 8) CTAs of a unit are one thread-block cluster.  Every CTA leaves its
+// partial in its own shared memory, the cluster synchronises, and rank 0 merges straight out of its
+// peers' shared memory (DSMEM): no partials through L2, no fence, no atomic, no second round trip —
+// the fixed cost that dominates decode calls of a few microseconds.  Same arithmetic in the same
+// order as the workspace merge: bit-equal results.
+template <int kD, bool kBf16, bool kPaged, bool kCluster = false>
 __global__ void __launch_bounds__(kThreads, 2)
 fa_decode_sm100(const DecodeParams p) {
+    using L = Smem<kD>;
     extern __shared__ __align__(128) uint8_t smem[];
     const int unit = blockIdx.x / p.nsplit, split = blockIdx.x - unit * p.nsplit;
     const int b = unit / p.heads_kv, kvh = unit - b * p.heads_kv;
@@ -525,13 +542,33 @@ fa_decode_sm100(const DecodeParams p) {
     const int key_end = min(seqlen, key_begin + p.chunk);
 
     attend_range<kD, kBf16, kPaged>(p, smem, b, kvh, key_begin, key_end);
-    const int64_t ubase = static_cast<int64_t>(unit) * p.nsplit;
-    write_range<kD, kBf16>(p, smem, b, kvh, p.nsplit == 1, ubase + split);
-    if (p.nsplit == 1) return;
-    arrive_and_merge<kD, kBf16>(p, smem, b, kvh, p.counters + unit, p.nsplit,
-                                [ubase](int i) { return ubase + i; });
+    if constexpr (kCluster) {
+        namespace cg = cooperative_groups;
+        cg::cluster_group cluster = cg::this_cluster();
+        float* own_o = reinterpret_cast<float*>(smem + L::kClusterO);
+        float* own_ml = reinterpret_cast<float*>(smem + L::kClusterML);
+        write_range<kD, kBf16>(p, smem, b, kvh, false, own_o, own_ml);
+        cluster.sync();  // every partial of the unit is in place (and visible cluster-wide)
+        if (split == 0)
+            merge_pieces<kD, kBf16, false>(
+                p, smem, b, kvh, p.nsplit,
+                [&](int i) { return static_cast<const float*>(cluster.map_shared_rank(own_ml, i)); },
+                [&](int i) { return static_cast<const float*>(cluster.map_shared_rank(own_o, i)); });
+        cluster.sync();  // a CTA's shared memory must outlive the reads of rank 0
+    } else {
+        const int64_t ubase = static_cast<int64_t>(unit) * p.nsplit;
+        write_range<kD, kBf16>(p, smem, b, kvh, p.nsplit == 1, p.part_o + (ubase + split) * kRows * kD,
+                               p.part_ml + (ubase + split) * kRows * 2);
+        if (p.nsplit == 1) return;
+        if (!arrive_last<kD>(smem, p.counters + unit, p.nsplit)) return;
+        const float* ml0 = p.part_ml + ubase * kRows * 2;
+        const float* o0 = p.part_o + ubase * kRows * kD;
+        merge_pieces<kD, kBf16, true>(
+            p, smem, b, kvh, p.nsplit, [ml0](int i) { return ml0 + i * kRows * 2; },
+            [o0](int i) { return o0 + static_cast<int64_t>(i) * kRows * kD; });
+        if (threadIdx.x == 0) p.counters[unit] = 0;  // re-arm for the next launch on this slot
+    }
 }
-
 
 // ---- paged K/V, the CTAs share the flattened key space -------------------------------------------
 // Unit u = (b, kvh) owns n(b) = max(1, ceil(len(b) / 64)) blocks of the line, units in (b, kvh)

@@ -706,9 +706,9 @@ struct DecodeVariant {
     int smem_bytes;
     std::once_flag attr_once[kMaxDevices];
 };
-template <int kD, bool kBf16, bool kPaged>
+template <int kD, bool kBf16, bool kPaged, bool kCluster = false>
 DecodeVariant* decode_variant() {
-    static DecodeVariant v{fa100::decode::fa_decode_sm100<kD, kBf16, kPaged>, fa100::decode::Smem<kD>::kTotal};
+    static DecodeVariant v{fa100::decode::fa_decode_sm100<kD, kBf16, kPaged, kCluster>, fa100::decode::Smem<kD>::kTotal};
     return &v;
 }
 template <int kD, bool kBf16>
@@ -726,6 +726,16 @@ DecodeVariant* pick_decode(int kd, bool bf16) {
     return kd == 128 ? (bf16 ? decode_variant<128, true, kPaged>() : decode_variant<128, false, kPaged>())
                      : (bf16 ? decode_variant<64, true, kPaged>() : decode_variant<64, false, kPaged>());
 }
+// The nsplit CTAs of a unit as one thread-block cluster, merged through DSMEM (2 <= nsplit <= 8).
+template <bool kPaged>
+DecodeVariant* pick_decode_cluster(int kd, bool bf16) {
+    return kd == 128 ? (bf16 ? decode_variant<128, true, kPaged, true>() : decode_variant<128, false, kPaged, true>())
+                     : (bf16 ? decode_variant<64, true, kPaged, true>() : decode_variant<64, false, kPaged, true>());
+}
+constexpr int kMaxClusterSplit = 8;  // portable cluster size
+inline bool cluster_merge(const DecodePlan& dp) {
+    return dp.flat_ctas == 0 && dp.nsplit >= 2 && dp.nsplit <= kMaxClusterSplit;
+}
 
 int check_workspace(const DecodePlan& dp, const void* workspace, int64_t workspace_bytes) {
     if (dp.nsplit == 1) return FA_SM100_OK;
@@ -742,7 +752,7 @@ int check_workspace(const DecodePlan& dp, const void* workspace, int64_t workspa
 }
 
 int launch_decode(DecodeVariant* var, fa100::decode::DecodeParams& kp, const DecodePlan& dp, DeviceState* st,
-                  int device, void* workspace, void* stream) {
+                  int device, void* workspace, void* stream, bool cluster = false) {
     cudaError_t attr_err = cudaSuccess;
     std::call_once(var->attr_once[device], [&] {
         attr_err = cudaFuncSetAttribute(reinterpret_cast<const void*>(var->fn),
@@ -761,8 +771,26 @@ int launch_decode(DecodeVariant* var, fa100::decode::DecodeParams& kp, const Dec
         kp.part_o = reinterpret_cast<float*>(ws + dp.ml_bytes);
     }
     const int grid = dp.flat_ctas > 0 ? dp.flat_ctas : dp.units * dp.nsplit;
-    var->fn<<<dim3(grid), dim3(fa100::decode::kThreads), var->smem_bytes, static_cast<cudaStream_t>(stream)>>>(kp);
-    cudaError_t e = cudaGetLastError();
+    cudaError_t e;
+    if (cluster) {
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3(grid);
+        cfg.blockDim = dim3(fa100::decode::kThreads);
+        cfg.dynamicSmemBytes = var->smem_bytes;
+        cfg.stream = static_cast<cudaStream_t>(stream);
+        cudaLaunchAttribute attr;
+        attr.id = cudaLaunchAttributeClusterDimension;
+        attr.val.clusterDim.x = dp.nsplit;
+        attr.val.clusterDim.y = 1;
+        attr.val.clusterDim.z = 1;
+        cfg.attrs = &attr;
+        cfg.numAttrs = 1;
+        e = cudaLaunchKernelEx(&cfg, var->fn, kp);
+    } else {
+        var->fn<<<dim3(grid), dim3(fa100::decode::kThreads), var->smem_bytes, static_cast<cudaStream_t>(stream)>>>(kp);
+        e = cudaGetLastError();
+    }
     if (e != cudaSuccess) return fail(FA_SM100_ERR_CUDA, "decode kernel launch: %s", cudaGetErrorString(e));
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return FA_SM100_OK;
@@ -809,8 +837,9 @@ extern "C" int fa_sm100_fwd_decode(const fa_sm100_fwd_params* p, void* workspace
     kp.v_sb = p->v_strides[0]; kp.v_sh = p->v_strides[1]; kp.v_ss = p->v_strides[2];
     kp.o_sb = p->o_strides[0]; kp.o_sh = p->o_strides[1];
     kp.scale_log2 = p->softmax_scale * 1.4426950408889634f;
-    return launch_decode(pick_decode<false>(dp.kd, p->dtype == FA_SM100_BF16), kp, dp, st, p->device,
-                         workspace, stream);
+    const bool bf16 = p->dtype == FA_SM100_BF16, cl = cluster_merge(dp);
+    return launch_decode(cl ? pick_decode_cluster<false>(dp.kd, bf16) : pick_decode<false>(dp.kd, bf16), kp, dp, st,
+                         p->device, workspace, stream, cl);
 }
 
 extern "C" int fa_sm100_paged_decode_plan(const fa_sm100_paged_decode_params* p, int32_t* nsplit,
@@ -854,9 +883,11 @@ extern "C" int fa_sm100_fwd_decode_paged(const fa_sm100_paged_decode_params* p, 
     for (int sh = 4; sh < 31; ++sh)
         if ((int64_t(1) << sh) == p->page_size) kp.page_shift = sh;
     kp.scale_log2 = p->softmax_scale * 1.4426950408889634f;
-    const bool bf16 = p->dtype == FA_SM100_BF16;
-    return launch_decode(dp.flat_ctas > 0 ? pick_decode_flat(dp.kd, bf16) : pick_decode<true>(dp.kd, bf16), kp, dp,
-                         st, p->device, workspace, stream);
+    const bool bf16 = p->dtype == FA_SM100_BF16, cl = cluster_merge(dp);
+    return launch_decode(dp.flat_ctas > 0 ? pick_decode_flat(dp.kd, bf16)
+                         : cl             ? pick_decode_cluster<true>(dp.kd, bf16)
+                                          : pick_decode<true>(dp.kd, bf16),
+                         kp, dp, st, p->device, workspace, stream, cl);
 }
 
 // ------------------------------------------------------------------------------------------------
