@@ -164,6 +164,43 @@ def test_decode_shape_changes_on_one_stream(cuda_device):
                      f"call {i}: B={B} units={B * Hkv} nsplit={plan['nsplit']}")
 
 
+@pytest.mark.gpu
+def test_decode_is_graph_capturable(cuda_device):
+    """Cluster launch (2 <= nsplit <= 8, merge through DSMEM), the L2 merge (nsplit > 8) and the
+    flattened paged kernel all record into a CUDA graph and replay to the eager bits."""
+    from flash_attention import flash_attn_decode_paged
+
+    ext = _ext()
+    cases = []
+    for B, Hq, Hkv, Sk in [(16, 64, 8, 1024), (1, 32, 8, 20000), (3, 16, 4, 2000)]:
+        q, k, v = make_qkv_fast(B, Hq, Hkv, 1, Sk, 128, torch.bfloat16, 70 + B, cuda_device)
+        assert (2 <= ext.decode_plan(q, k, k)["nsplit"] <= 8) == (B != 1)
+        cases.append(lambda q=q, k=k, v=v: ext.flash_attention_fwd(q, k, v, 128 ** -0.5, False))
+    pq, kc, vc, bt, sl, _, _ = _paged_case(6, 32, 8, 128, 64, [3000, 10, 0, 777, 64, 1500], torch.bfloat16,
+                                           cuda_device, 9)
+    cases.append(lambda: flash_attn_decode_paged(pq, kc, vc, bt, sl, max_seqlen_k=3000))
+    cases.append(lambda: flash_attn_decode_paged(pq, kc, vc, bt, sl, max_seqlen_k=3000, one_wave=True))
+    eager = [fn() for fn in cases]   # also creates the per-stream workspaces outside the capture
+    torch.cuda.synchronize()
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        for fn in cases:
+            fn()
+        s.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            outs = [fn() for fn in cases]
+    for _ in range(3):
+        for o in outs:
+            o.zero_()
+        g.replay()
+        torch.cuda.synchronize()
+        for i, (o, e) in enumerate(zip(outs, eager)):
+            assert torch.equal(o, e), f"case {i}"
+    from flash_attention_cute_b200 import _lib
+    _lib.check_device(0)
+
+
 # ------------------------------------------------------------------ paged KV cache
 def _paged_case(B, Hq, Hkv, D, page, lens, dtype, device, seed, layout="pshd", shared=False):
     """Random pages in random order; returns (q, k_cache, v_cache, block_table, seqlens, dense k, dense v)."""
