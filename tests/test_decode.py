@@ -358,6 +358,35 @@ def test_paged_decode_flattened_key_space(cuda_device, name):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("one_wave", [False, True], ids=["flat", "one_wave"])
+def test_paged_decode_page_size_not_a_power_of_two(cuda_device, one_wave):
+    """48- and 80-key pages: the kernels fall back from shifts to divisions (page_shift = -1)."""
+    from flash_attention import flash_attn_decode_paged
+
+    for page, lens in [(48, [1000, 47, 48, 49, 0, 2500]), (80, [81, 4000, 160])]:
+        q, kc, vc, bt, sl, dk, dv = _paged_case(len(lens), 16, 4, 128, page, lens, torch.bfloat16, cuda_device, 21)
+        out = flash_attn_decode_paged(q, kc, vc, bt, sl, max_seqlen_k=max(lens), one_wave=one_wave)
+        for b, n in enumerate(lens):
+            if n == 0:
+                assert not out[b].any()
+                continue
+            ref = eager_attention(q[b:b + 1].unsqueeze(2), dk[b:b + 1, :, :n], dv[b:b + 1, :, :n], None, False,
+                                  out_dtype=torch.float32)
+            assert_close(out[b:b + 1].unsqueeze(2), ref, torch.bfloat16, f"page {page} seq {b} len {n}")
+
+
+@pytest.mark.gpu
+def test_paged_decode_exactly_as_many_sequences_as_the_flat_kernel_takes(cuda_device):
+    """B = 2048: the prefix sums fill the shared-memory array to its last entry."""
+    import random
+
+    rng = random.Random(6)
+    lens = [rng.randrange(0, 130) for _ in range(2048)]
+    lens[-1] = 129
+    _check_paged(cuda_device, 2048, 4, 1, 128, 16, lens, torch.bfloat16, 12, sample=[0, 1, 1023, 2046, 2047])
+
+
+@pytest.mark.gpu
 def test_paged_decode_more_sequences_than_the_flat_kernel_takes(cuda_device):
     """B > 2048: one CTA per unit (fa_decode_sm100<paged>), lengths still per sequence."""
     import random
