@@ -1,4 +1,4 @@
-// fa_sm100_decode.cuh — split-KV decode kernel (Sq == 1) for B200.
+// fa_sm100_decode.cuh — split-KV decode kernels (Sq == 1) for B200.
 //
 // SURVEY §8(f) rank 2.  The reference handles a single query position by packing the q heads of a
 // kv group into the rows of one M tile and running the prefill kernel, one CTA per (batch, kv-head)
@@ -20,9 +20,13 @@
 //     registers (fp32 state, row sum from unrounded P, P rounded to T before P·V — the same
 //     numerics as the prefill kernel), O += P·V (V fragments by ldmatrix.trans).  The 5th-gen
 //     tensor cores (tcgen05, M >= 64) have nothing to offer a 16-row problem that is HBM-bound.
-//   * the four warps merge (m, l, O) through shared memory; with nsplit > 1 the CTA writes its
-//     partial to the workspace and the last CTA of a unit to arrive (one atomic counter per unit)
-//     merges the splits and writes O — one launch, no second kernel.
+//   * the four warps merge (m, l, O) through shared memory; with nsplit > 1 the splits of a unit
+//     are merged inside the same launch: 2 .. 8 splits run as one thread-block cluster and rank 0
+//     reads its peers' partials out of their shared memory (DSMEM); beyond that each CTA writes its
+//     partial to the workspace and the last CTA of the unit to arrive (one atomic counter per
+//     unit) merges them.
+//   * 16 copies a lane and tile: everything about their addresses that does not change from tile
+//     to tile is computed once (TileCopy) — the loop was issue-bound on address arithmetic.
 //   * paged KV with per-sequence lengths (fa_decode_flat_sm100): the host cannot size a split per
 //     sequence (the lengths are device data), so the CTAs of one wave share the FLATTENED key space
 //     instead: every (batch, kv-head) unit owns ceil(len / 64) blocks of 64 keys, laid end to end,

@@ -110,7 +110,9 @@ int fa_sm100_fwd(const fa_sm100_fwd_params* params, void* stream);
  * (0 bytes when nsplit == 1).  The caller owns the workspace: 256-byte aligned device memory that
  * holds the partial results of the launch only — no state survives a launch and nothing has to be
  * zeroed, so one buffer (of the largest size any call needs) serves all stream-ordered launches
- * of any shape.  The per-unit arrival counters live in a library-owned ring. */
+ * of any shape.  The per-unit arrival counters live in a library-owned ring.  (With 2 .. 8 splits
+ * the CTAs of a unit run as one thread-block cluster and merge through distributed shared memory;
+ * the workspace of the plan is then not touched, but the contract stays: pass what the plan asks.) */
 int fa_sm100_decode_plan(const fa_sm100_fwd_params* params, int32_t* nsplit, int32_t* chunk_keys,
                          int64_t* workspace_bytes);
 int fa_sm100_fwd_decode(const fa_sm100_fwd_params* params, void* workspace, int64_t workspace_bytes,
