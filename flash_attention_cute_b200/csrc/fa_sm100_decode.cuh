@@ -528,6 +528,12 @@ __device__ __forceinline__ void merge_pieces(const DecodeParams& p, uint8_t* sme
     __syncthreads();
 }
 
+// Keys of sequence b of a paged batch.  The contract is 0 <= seqlens[b] <= max_seqlen_k (the block
+// table is only that wide); a value outside it is clamped rather than followed out of the table.
+__device__ __forceinline__ int paged_len(const DecodeParams& p, int b) {
+    return min(max(__ldg(p.seqlens + b), 0), p.seqlen_k);
+}
+
 // ---- one CTA per (unit, split): contiguous K/V, or paged K/V with the per-sequence split ---------
 // kCluster: the nsplit (2 .. 8) CTAs of a unit are one thread-block cluster.  Every CTA leaves its
 // partial in its own shared memory, the cluster synchronises, and rank 0 merges straight out of its
@@ -542,7 +548,7 @@ fa_decode_sm100(const DecodeParams p) {
     const int unit = blockIdx.x / p.nsplit, split = blockIdx.x - unit * p.nsplit;
     const int b = unit / p.heads_kv, kvh = unit - b * p.heads_kv;
     const int key_begin = split * p.chunk;
-    const int seqlen = kPaged ? p.seqlens[b] : p.seqlen_k;
+    const int seqlen = kPaged ? paged_len(p, b) : p.seqlen_k;
     const int key_end = min(seqlen, key_begin + p.chunk);
 
     attend_range<kD, kBf16, kPaged>(p, smem, b, kvh, key_begin, key_end);
@@ -624,7 +630,7 @@ fa_decode_flat_sm100(const DecodeParams p) {
         const int per = (B + kThreads - 1) / kThreads;
         const int first = threadIdx.x * per, last = min(B, first + per);
         int sum = 0;
-        for (int i = first; i < last; ++i) sum += max(1, (__ldg(p.seqlens + i) + kFlatBlock - 1) / kFlatBlock);
+        for (int i = first; i < last; ++i) sum += max(1, (paged_len(p, i) + kFlatBlock - 1) / kFlatBlock);
         int incl = sum;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
@@ -638,7 +644,7 @@ fa_decode_flat_sm100(const DecodeParams p) {
         for (int w = 0; w < warp; ++w) base += wtot[w];
         for (int i = first; i < last; ++i) {
             pre[i] = base;
-            base += max(1, (__ldg(p.seqlens + i) + kFlatBlock - 1) / kFlatBlock);
+            base += max(1, (paged_len(p, i) + kFlatBlock - 1) / kFlatBlock);
         }
         if (threadIdx.x == kThreads - 1) pre[B] = base;  // the last thread's run ends the line (or is empty)
         __syncthreads();
@@ -662,7 +668,7 @@ fa_decode_flat_sm100(const DecodeParams p) {
         cc.n = pre[lo + 1] - pre[lo];
         cc.kvh = (start - Hkv * pre[lo]) / cc.n;
         cc.blk = start - Hkv * pre[lo] - cc.kvh * cc.n;
-        cc.len = __ldg(p.seqlens + lo);
+        cc.len = paged_len(p, lo);
     }
     FlatCursor ic = cc;  // the copies run two blocks ahead of the math
     auto advance = [&](FlatCursor& c) {
@@ -672,7 +678,7 @@ fa_decode_flat_sm100(const DecodeParams p) {
         c.kvh = 0;
         if (++c.b < B) {
             c.n = pre[c.b + 1] - pre[c.b];
-            c.len = __ldg(p.seqlens + c.b);
+            c.len = paged_len(p, c.b);
         } else {
             c.n = 1;  // past the line: never issued, never computed
             c.len = 0;

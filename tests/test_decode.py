@@ -376,6 +376,23 @@ def test_paged_decode_page_size_not_a_power_of_two(cuda_device, one_wave):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("one_wave", [False, True], ids=["flat", "one_wave"])
+def test_paged_decode_clamps_lengths_outside_the_contract(cuda_device, one_wave):
+    """seqlens_k[b] > max_seqlen_k or < 0 breaks the contract; the kernels clamp instead of
+    walking out of the block table: the result is that of the clamped lengths."""
+    from flash_attention import flash_attn_decode_paged
+
+    lens = [1000, 700, 333, 1000]
+    q, kc, vc, bt, sl, dk, dv = _paged_case(4, 16, 4, 128, 64, lens, torch.bfloat16, cuda_device, 33)
+    good = flash_attn_decode_paged(q, kc, vc, bt, sl, max_seqlen_k=1000, one_wave=one_wave)
+    bad = torch.tensor([50000, 700, -7, 1000], dtype=torch.int32, device=cuda_device)
+    out = flash_attn_decode_paged(q, kc, vc, bt, bad, max_seqlen_k=1000, one_wave=one_wave)
+    for b in (0, 1, 3):   # (the flattened split points move with the total: close, not bit-equal)
+        assert_close(out[b:b + 1], good[b:b + 1].float(), torch.bfloat16, f"seq {b}")
+    assert not out[2].any()
+
+
+@pytest.mark.gpu
 def test_paged_decode_exactly_as_many_sequences_as_the_flat_kernel_takes(cuda_device):
     """B = 2048: the prefix sums fill the shared-memory array to its last entry."""
     import random
